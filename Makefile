@@ -1,0 +1,27 @@
+# Builds libcurvefit_cuda.so (sm_100a only) in-tree with nvcc; the CMake build
+# (CMakeLists.txt) produces the same library.  `make oracle` builds the CPU
+# restatement used by the tests.
+NVCC     ?= nvcc
+ARCH     := -gencode arch=compute_100a,code=sm_100a
+NVFLAGS  := $(ARCH) -O3 -lineinfo -std=c++17 -Iinclude -Xcompiler -fPIC,-fvisibility=hidden \
+            -Xptxas -v -ccbin /usr/bin/g++
+SRC      := $(wildcard curvefit_b200/csrc/*.cu)
+OBJ      := $(patsubst curvefit_b200/csrc/%.cu,build/%.o,$(SRC))
+LIB      := curvefit_b200/libcurvefit_cuda.so
+
+all: $(LIB)
+
+build/%.o: curvefit_b200/csrc/%.cu curvefit_b200/csrc/common.cuh include/curvefit_cuda.h
+	@mkdir -p build
+	$(NVCC) $(NVFLAGS) -c $< -o $@
+
+$(LIB): $(OBJ)
+	$(NVCC) $(ARCH) -shared -o $@ $(OBJ) -lcudart -ccbin /usr/bin/g++
+
+oracle:
+	$(MAKE) -C oracle
+
+clean:
+	rm -rf build $(LIB)
+
+.PHONY: all oracle clean

@@ -1,0 +1,601 @@
+// api.cu -- the C ABI of libcurvefit_cuda (include/curvefit_cuda.h): handle
+// lifecycle, the lowess driver loop (src/curvefit_regression.f90:657-714 as a
+// chain of device stages), and the stateless host-buffer entry points the
+// Fortran shim binds.  No CPU fallback: every entry point that does work needs
+// a CUDA device and reports CF_DEVICE_ERROR otherwise.
+#include <math.h>
+#include <stdarg.h>
+#include <string.h>
+
+#include <new>
+#include <vector>
+
+#include "common.cuh"
+
+namespace cf {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line)
+{
+    set_error("CUDA error %d (%s) in %s at %s:%d", (int)e, cudaGetErrorString(e), what, file, line);
+    return e == cudaErrorMemoryAllocation ? CF_OUT_OF_MEMORY_ERROR : CF_DEVICE_ERROR;
+}
+
+constexpr int kTile = 512;  // fit.cu's T = NT*P; shard blocks are multiples of it
+
+static void compute_shard(cf_lowess* h)
+{
+    const int64_t n = h->n;
+    int64_t per = (n + h->nranks - 1) / h->nranks;
+    per = (per + kTile - 1) / kTile * kTile;
+    if (per < kTile) per = kTile;
+    h->block = (int32_t)per;
+    const int64_t b = (int64_t)h->rank * per;
+    h->begin = (int32_t)(b < n ? b : n);
+    h->end = (int32_t)(b + per < n ? b + per : n);
+}
+
+static void free_buffers(cf_lowess* h)
+{
+    cudaFree(h->x); cudaFree(h->y); cudaFree(h->ys); cudaFree(h->rw); cudaFree(h->res);
+    cudaFree(h->win.nleft); cudaFree(h->win.lo9); cudaFree(h->win.hi9);
+    cudaFree(h->win.lo1); cudaFree(h->win.hi1); cudaFree(h->win.leader);
+    h->x = h->y = h->ys = h->rw = h->res = nullptr;
+    h->win = Windows{};
+    h->cap = h->cap_rw = 0;
+}
+
+static int reserve(cf_lowess* h, int32_t n)
+{
+    const int64_t need = n > 0 ? n : 1;
+    if (need > h->cap) {
+        free_buffers(h);
+        const size_t bd = sizeof(double) * (size_t)need, bi = sizeof(int32_t) * (size_t)need;
+        CF_CUDA(cudaMalloc(&h->x, bd));
+        CF_CUDA(cudaMalloc(&h->y, bd));
+        CF_CUDA(cudaMalloc(&h->ys, bd));
+        CF_CUDA(cudaMalloc(&h->res, bd));
+        CF_CUDA(cudaMalloc(&h->win.nleft, bi));
+        CF_CUDA(cudaMalloc(&h->win.lo9, bi));
+        CF_CUDA(cudaMalloc(&h->win.hi9, bi));
+        CF_CUDA(cudaMalloc(&h->win.lo1, bi));
+        CF_CUDA(cudaMalloc(&h->win.hi1, bi));
+        CF_CUDA(cudaMalloc(&h->win.leader, bi));
+        h->cap = need;
+    }
+    return CF_OK;
+}
+
+// rw is padded to nranks * block so that an all-gather of equal blocks fits
+static int reserve_rw(cf_lowess* h)
+{
+    int64_t need = (int64_t)h->nranks * h->block;
+    if (need < h->n) need = h->n;
+    if (need < 1) need = 1;
+    if (need > h->cap_rw) {
+        cudaFree(h->rw);
+        h->rw = nullptr;
+        h->cap_rw = 0;
+        CF_CUDA(cudaMalloc(&h->rw, sizeof(double) * (size_t)need));
+        CF_CUDA(cudaMemsetAsync(h->rw, 0, sizeof(double) * (size_t)need, h->stream));
+        h->cap_rw = need;
+    }
+    return CF_OK;
+}
+
+static int use_device(const cf_lowess* h)
+{
+    CF_CUDA(cudaSetDevice(h->device));
+    return CF_OK;
+}
+
+static int robust_update(cf_lowess* h)
+{
+    CF_TRY(launch_select_reset(h));
+    for (int r = 0; r < kSelRounds; ++r) {
+        CF_TRY(launch_hist(h, r));
+        CF_TRY(launch_pick(h, r));
+    }
+    return launch_bisquare(h);
+}
+
+static int begin_stage(cf_lowess* h, double f)
+{
+    if (!h->init) { set_error("No data has been defined."); return CF_NO_DATA_DEFINED_ERROR; }
+    if (!(f == f)) { set_error("f is NaN"); return CF_INVALID_INPUT_ERROR; }
+    const int32_t ns = cf_lowess_span(h->n, f);
+    if (h->n >= 2 && (h->win_f != f || h->ns != ns)) {
+        h->ns = ns;
+        CF_TRY(launch_windows(h, ns));
+        h->win_f = f;
+    }
+    h->ns = ns;
+    return CF_OK;
+}
+
+}  // namespace cf
+
+using namespace cf;
+
+extern "C" {
+
+int32_t cf_version(void) { return 100; }
+
+int32_t cf_last_error(char* buf, int32_t len)
+{
+    const int32_t need = (int32_t)strlen(g_err);
+    if (buf && len > 0) {
+        strncpy(buf, g_err, (size_t)len - 1);
+        buf[len - 1] = '\0';
+    }
+    return need;
+}
+
+int32_t cf_lowess_span(int32_t n, double f)
+{
+    // ns = max(min(int(f * real(n)), n), 2), src/curvefit_regression.f90:647
+    const double fn = f * (double)n;
+    int32_t k;
+    if (!(fn < 2147483647.0)) k = n;
+    else if (fn < -2147483647.0) k = 2;
+    else k = (int32_t)fn;
+    if (k > n) k = n;
+    if (k < 2) k = 2;
+    return k;
+}
+
+int32_t cf_lowess_select_rounds(void) { return kSelRounds; }
+int32_t cf_lowess_hist_len(void) { return kHistLen; }
+
+int32_t cf_lowess_create(cf_lowess** out, int32_t device, void* stream)
+{
+    if (!out) { set_error("null handle pointer"); return CF_INVALID_INPUT_ERROR; }
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        set_error("no CUDA device available (%s); libcurvefit_cuda has no CPU fallback",
+                  e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+        return CF_DEVICE_ERROR;
+    }
+    if (device < 0) CF_CUDA(cudaGetDevice(&device));
+    if (device >= ndev) { set_error("device %d out of range (%d)", device, ndev); return CF_INVALID_INPUT_ERROR; }
+    CF_CUDA(cudaSetDevice(device));
+    cf_lowess* h = new (std::nothrow) cf_lowess();
+    if (!h) { set_error("Insufficient memory available."); return CF_OUT_OF_MEMORY_ERROR; }
+    h->device = device;
+    if (stream) {
+        h->stream = (cudaStream_t)stream;
+    } else {
+        e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+        if (e != cudaSuccess) { delete h; return cuda_fail(e, "cudaStreamCreate", __FILE__, __LINE__); }
+        h->own_stream = true;
+    }
+    for (auto& ev : h->ev) {
+        e = cudaEventCreate(&ev);
+        if (e != cudaSuccess) { cf_lowess_destroy(h); return cuda_fail(e, "cudaEventCreate", __FILE__, __LINE__); }
+    }
+    e = cudaMalloc(&h->hist, sizeof(unsigned long long) * kHistLen);
+    if (e == cudaSuccess) e = cudaMalloc(&h->sel, sizeof(SelectState));
+    if (e == cudaSuccess) e = cudaMemsetAsync(h->hist, 0, sizeof(unsigned long long) * kHistLen, h->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(h->sel, 0, sizeof(SelectState), h->stream);
+    if (e != cudaSuccess) { cf_lowess_destroy(h); return cuda_fail(e, "cudaMalloc(select)", __FILE__, __LINE__); }
+    *out = h;
+    return CF_OK;
+}
+
+void cf_lowess_destroy(cf_lowess* h)
+{
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    free_buffers(h);
+    cudaFree(h->hist);
+    cudaFree(h->sel);
+    for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
+    if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+static int32_t init_common(cf_lowess* h, const void* x, const void* y, int32_t n, int32_t sort,
+                           cudaMemcpyKind kind)
+{
+    if (!h) { set_error("null handle"); return CF_INVALID_INPUT_ERROR; }
+    if (n < 0 || (n > 0 && (!x || !y))) { set_error("Input array sizes must match."); return CF_ARRAY_SIZE_ERROR; }
+    CF_TRY(use_device(h));
+    h->init = false;                                   // :758
+    h->win_f = -1.0;
+    CF_TRY(reserve(h, n));
+    h->n = n;
+    compute_shard(h);
+    CF_TRY(reserve_rw(h));
+    const size_t bytes = sizeof(double) * (size_t)n;
+    if (n > 0) {
+        if (sort) {
+            // stage the unsorted input in ys/res, sort into x/y  (:793-798)
+            CF_CUDA(cudaMemcpyAsync(h->ys, x, bytes, kind, h->stream));
+            CF_CUDA(cudaMemcpyAsync(h->res, y, bytes, kind, h->stream));
+            CF_TRY(sort_xy_device(h->ys, h->res, n, h->x, h->y, nullptr, h->stream, &h->launches));
+        } else {
+            CF_CUDA(cudaMemcpyAsync(h->x, x, bytes, kind, h->stream));   // :800-803
+            CF_CUDA(cudaMemcpyAsync(h->y, y, bytes, kind, h->stream));
+        }
+        CF_CUDA(cudaStreamSynchronize(h->stream));
+    }
+    h->init = true;                                    // :810
+    return CF_OK;
+}
+
+int32_t cf_lowess_init(cf_lowess* h, const double* x, const double* y, int32_t n, int32_t sort)
+{
+    return init_common(h, x, y, n, sort, cudaMemcpyHostToDevice);
+}
+
+int32_t cf_lowess_init_device(cf_lowess* h, const void* d_x, const void* d_y, int32_t n, int32_t sort)
+{
+    return init_common(h, d_x, d_y, n, sort, cudaMemcpyDeviceToDevice);
+}
+
+int32_t cf_lowess_set_shard(cf_lowess* h, int32_t rank, int32_t nranks)
+{
+    if (!h || nranks < 1 || rank < 0 || rank >= nranks) { set_error("bad shard %d of %d", rank, nranks); return CF_INVALID_INPUT_ERROR; }
+    CF_TRY(use_device(h));
+    h->rank = rank;
+    h->nranks = nranks;
+    compute_shard(h);
+    return reserve_rw(h);
+}
+
+int32_t cf_lowess_shard(const cf_lowess* h, int32_t* begin, int32_t* end, int32_t* block)
+{
+    if (!h) return CF_INVALID_INPUT_ERROR;
+    if (begin) *begin = h->begin;
+    if (end) *end = h->end;
+    if (block) *block = h->block;
+    return CF_OK;
+}
+
+int32_t cf_lowess_count(const cf_lowess* h) { return (h && h->init) ? h->n : 0; }
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------
+// the driver loop and the rest of the ABI
+// ---------------------------------------------------------------------------
+extern "C" {
+
+// `passes` fit passes; the first uses rw iff first_uses_rw (lowess :657-714)
+static int32_t run_passes(cf_lowess* h, int32_t passes, bool first_uses_rw, cf_stats* st)
+{
+    std::vector<cudaEvent_t> evs;
+    const bool timed = st != nullptr;
+    auto mark = [&]() -> int {
+        if (!timed) return CF_OK;
+        cudaEvent_t e;
+        CF_CUDA(cudaEventCreate(&e));
+        evs.push_back(e);
+        CF_CUDA(cudaEventRecord(e, h->stream));
+        return CF_OK;
+    };
+    int rc = CF_OK;
+    bool use_rw = first_uses_rw;
+    for (int32_t p = 0; p < passes && rc == CF_OK; ++p) {          // :657
+        if ((rc = mark()) != CF_OK) break;
+        if ((rc = launch_fit(h, use_rw)) != CF_OK) break;          // :662-693
+        if ((rc = mark()) != CF_OK) break;
+        if ((rc = launch_residuals(h)) != CF_OK) break;            // :695
+        if (p + 1 < passes) {                                      // :696
+            if ((rc = robust_update(h)) != CF_OK) break;           // :697-713
+            use_rw = true;
+        }
+    }
+    if (rc == CF_OK) rc = mark();
+    if (rc == CF_OK) {
+        cudaError_t e = cudaStreamSynchronize(h->stream);
+        if (e != cudaSuccess) rc = cuda_fail(e, "lowess passes", __FILE__, __LINE__);
+    }
+    if (rc == CF_OK && timed) {
+        // events: [fit0 start, fit0 end, fit1 start, fit1 end, ..., final]
+        float fit = 0.f, rob = 0.f, ms = 0.f;
+        for (size_t k = 0; k + 1 < evs.size(); ++k) {
+            cudaEventElapsedTime(&ms, evs[k], evs[k + 1]);
+            if (k % 2 == 0) fit += ms; else rob += ms;
+        }
+        st->ms_fit = fit;
+        st->ms_robust = rob;
+    }
+    for (cudaEvent_t e : evs) cudaEventDestroy(e);
+    return rc;
+}
+
+int32_t cf_lowess_run(cf_lowess* h, double f, int32_t nsteps, cf_stats* st)
+{
+    if (!h) { set_error("null handle"); return CF_INVALID_INPUT_ERROR; }
+    if (nsteps < 0) { set_error("nsteps must be >= 0"); return CF_INVALID_INPUT_ERROR; }
+    CF_TRY(use_device(h));
+    if (st) memset(st, 0, sizeof(*st));
+    const int l0 = h->launches, f0 = h->fit_launches;
+    CF_CUDA(cudaEventRecord(h->ev[0], h->stream));
+    CF_TRY(begin_stage(h, f));
+    CF_CUDA(cudaEventRecord(h->ev[1], h->stream));
+    if (h->n < 2) {                                                 // :651-654
+        if (h->n == 1) CF_CUDA(cudaMemcpyAsync(h->ys, h->y, sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+        CF_CUDA(cudaStreamSynchronize(h->stream));
+    } else {
+        CF_TRY(run_passes(h, nsteps + 1, false, st));
+    }
+    CF_CUDA(cudaEventRecord(h->ev[2], h->stream));
+    CF_CUDA(cudaEventSynchronize(h->ev[2]));
+    if (st) {
+        cudaEventElapsedTime(&st->ms_total, h->ev[0], h->ev[2]);
+        cudaEventElapsedTime(&st->ms_windows, h->ev[0], h->ev[1]);
+        st->launches = h->launches - l0;
+        st->fit_launches = h->fit_launches - f0;
+        st->ns = h->ns;
+        st->passes = nsteps + 1;
+        if (nsteps > 0 && h->n >= 2) {
+            SelectState s;
+            CF_CUDA(cudaMemcpy(&s, h->sel, sizeof(s), cudaMemcpyDeviceToHost));
+            st->cmad_last = s.cmad;
+        }
+    }
+    return CF_OK;
+}
+
+int32_t cf_lowess_run_from_rw(cf_lowess* h, double f, const double* rw_in, int32_t passes)
+{
+    if (!h) { set_error("null handle"); return CF_INVALID_INPUT_ERROR; }
+    if (passes < 1) { set_error("passes must be >= 1"); return CF_INVALID_INPUT_ERROR; }
+    CF_TRY(use_device(h));
+    CF_TRY(begin_stage(h, f));
+    if (h->n < 2) { set_error("n < 2"); return CF_INVALID_INPUT_ERROR; }
+    if (rw_in)
+        CF_CUDA(cudaMemcpyAsync(h->rw, rw_in, sizeof(double) * (size_t)h->n, cudaMemcpyHostToDevice, h->stream));
+    return run_passes(h, passes, rw_in != nullptr, nullptr);
+}
+
+int32_t cf_lowess_fetch(cf_lowess* h, double* ys, double* rw, double* res)
+{
+    if (!h || !h->init) { set_error("No data has been defined."); return CF_NO_DATA_DEFINED_ERROR; }
+    CF_TRY(use_device(h));
+    const size_t bytes = sizeof(double) * (size_t)h->n;
+    if (ys) CF_CUDA(cudaMemcpyAsync(ys, h->ys, bytes, cudaMemcpyDeviceToHost, h->stream));
+    if (rw) CF_CUDA(cudaMemcpyAsync(rw, h->rw, bytes, cudaMemcpyDeviceToHost, h->stream));
+    if (res) CF_CUDA(cudaMemcpyAsync(res, h->res, bytes, cudaMemcpyDeviceToHost, h->stream));
+    CF_CUDA(cudaStreamSynchronize(h->stream));
+    return CF_OK;
+}
+
+int32_t cf_lowess_fetch_xy(cf_lowess* h, double* xs, double* ysrt)
+{
+    if (!h || !h->init) { set_error("No data has been defined."); return CF_NO_DATA_DEFINED_ERROR; }
+    CF_TRY(use_device(h));
+    const size_t bytes = sizeof(double) * (size_t)h->n;
+    if (xs) CF_CUDA(cudaMemcpyAsync(xs, h->x, bytes, cudaMemcpyDeviceToHost, h->stream));
+    if (ysrt) CF_CUDA(cudaMemcpyAsync(ysrt, h->y, bytes, cudaMemcpyDeviceToHost, h->stream));
+    CF_CUDA(cudaStreamSynchronize(h->stream));
+    return CF_OK;
+}
+
+__global__ void plus_one_kernel(const int32_t* __restrict__ in, int32_t* __restrict__ out,
+                                int32_t n, int32_t add)
+{
+    const int32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = in[i] + add;
+}
+
+int32_t cf_lowess_windows(cf_lowess* h, double f, int32_t* nleft, int32_t* nright, int32_t* lo9,
+                          int32_t* hi9, int32_t* lo1, int32_t* hi1, int32_t* leader)
+{
+    if (!h) { set_error("null handle"); return CF_INVALID_INPUT_ERROR; }
+    CF_TRY(use_device(h));
+    CF_TRY(begin_stage(h, f));
+    if (h->n < 2) return CF_OK;
+    const int32_t n = h->n;
+    int32_t* tmp = nullptr;
+    CF_CUDA(cudaMalloc(&tmp, sizeof(int32_t) * (size_t)n));
+    struct { const int32_t* src; int32_t* dst; int32_t add; } jobs[] = {
+        {h->win.nleft, nleft, 1}, {h->win.nleft, nright, h->ns},   // nright = nleft + ns - 1
+        {h->win.lo9, lo9, 1},     {h->win.hi9, hi9, 1},
+        {h->win.lo1, lo1, 1},     {h->win.hi1, hi1, 1},
+        {h->win.leader, leader, 1},
+    };
+    int rc = CF_OK;
+    for (auto& j : jobs) {
+        if (!j.dst) continue;
+        plus_one_kernel<<<(n + 255) / 256, 256, 0, h->stream>>>(j.src, tmp, n, j.add);
+        cudaError_t e = cudaMemcpyAsync(j.dst, tmp, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost, h->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+        if (e != cudaSuccess) { rc = cuda_fail(e, "windows fetch", __FILE__, __LINE__); break; }
+    }
+    cudaFree(tmp);
+    return rc;
+}
+
+// ---- stage API -----------------------------------------------------------------
+int32_t cf_lowess_stage_begin(cf_lowess* h, double f)
+{
+    if (!h) return CF_INVALID_INPUT_ERROR;
+    CF_TRY(use_device(h));
+    CF_TRY(begin_stage(h, f));
+    if (h->n < 2) { set_error("n < 2"); return CF_INVALID_INPUT_ERROR; }
+    return launch_select_reset(h);
+}
+int32_t cf_lowess_stage_fit(cf_lowess* h, int32_t use_rw)
+{
+    if (!h || !h->init) return CF_NO_DATA_DEFINED_ERROR;
+    CF_TRY(use_device(h));
+    CF_TRY(launch_fit(h, use_rw != 0));
+    CF_TRY(launch_residuals(h));
+    return launch_select_reset(h);
+}
+int32_t cf_lowess_stage_hist(cf_lowess* h, int32_t round)
+{
+    if (!h || !h->init || round < 0 || round >= kSelRounds) return CF_INVALID_INPUT_ERROR;
+    CF_TRY(use_device(h));
+    return launch_hist(h, round);
+}
+int32_t cf_lowess_stage_pick(cf_lowess* h, int32_t round)
+{
+    if (!h || !h->init || round < 0 || round >= kSelRounds) return CF_INVALID_INPUT_ERROR;
+    CF_TRY(use_device(h));
+    return launch_pick(h, round);
+}
+int32_t cf_lowess_stage_weights(cf_lowess* h)
+{
+    if (!h || !h->init) return CF_NO_DATA_DEFINED_ERROR;
+    CF_TRY(use_device(h));
+    return launch_bisquare(h);
+}
+int32_t cf_lowess_sync(cf_lowess* h)
+{
+    if (!h) return CF_INVALID_INPUT_ERROR;
+    CF_TRY(use_device(h));
+    CF_CUDA(cudaStreamSynchronize(h->stream));
+    return CF_OK;
+}
+
+void* cf_lowess_buffer(cf_lowess* h, int32_t which)
+{
+    if (!h) return nullptr;
+    switch (which) {
+        case CF_BUF_X: return h->x;
+        case CF_BUF_Y: return h->y;
+        case CF_BUF_YS: return h->ys;
+        case CF_BUF_RW: return h->rw;
+        case CF_BUF_RES: return h->res;
+        case CF_BUF_HIST: return h->hist;
+        case CF_BUF_CMAD: return &h->sel->cmad;
+        default: return nullptr;
+    }
+}
+
+int32_t cf_fp64_peak(int32_t device, double ms_target, double* tflops, double* sm_mhz_est)
+{
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        set_error("no CUDA device available");
+        return CF_DEVICE_ERROR;
+    }
+    return fp64_peak(device, ms_target, tflops, sm_mhz_est);
+}
+
+// ---- stateless host-buffer entry points -------------------------------------------
+int32_t cf_sort_xy(const double* x, const double* y, int32_t n, double* x_sorted,
+                   double* y_sorted, int32_t* perm)
+{
+    if (n < 0 || (n > 0 && (!x || !y || !x_sorted || !y_sorted))) {
+        set_error("Input array sizes must match.");
+        return CF_ARRAY_SIZE_ERROR;
+    }
+    if (n == 0) return CF_OK;
+    cf_lowess* h = nullptr;
+    CF_TRY(cf_lowess_create(&h, -1, nullptr));
+    int rc = CF_OK;
+    double *dx = nullptr, *dy = nullptr, *ox = nullptr, *oy = nullptr;
+    int32_t* dp = nullptr;
+    const size_t bytes = sizeof(double) * (size_t)n;
+    cudaError_t e = cudaMalloc(&dx, bytes);
+    if (e == cudaSuccess) e = cudaMalloc(&dy, bytes);
+    if (e == cudaSuccess) e = cudaMalloc(&ox, bytes);
+    if (e == cudaSuccess) e = cudaMalloc(&oy, bytes);
+    if (e == cudaSuccess && perm) e = cudaMalloc(&dp, sizeof(int32_t) * (size_t)n);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dx, x, bytes, cudaMemcpyHostToDevice, h->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dy, y, bytes, cudaMemcpyHostToDevice, h->stream);
+    if (e != cudaSuccess) rc = cuda_fail(e, "cf_sort_xy upload", __FILE__, __LINE__);
+    if (rc == CF_OK) rc = sort_xy_device(dx, dy, n, ox, oy, dp, h->stream, &h->launches);
+    if (rc == CF_OK) {
+        e = cudaMemcpyAsync(x_sorted, ox, bytes, cudaMemcpyDeviceToHost, h->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(y_sorted, oy, bytes, cudaMemcpyDeviceToHost, h->stream);
+        if (e == cudaSuccess && perm) e = cudaMemcpyAsync(perm, dp, sizeof(int32_t) * (size_t)n, cudaMemcpyDeviceToHost, h->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+        if (e != cudaSuccess) rc = cuda_fail(e, "cf_sort_xy download", __FILE__, __LINE__);
+    }
+    cudaFree(dx); cudaFree(dy); cudaFree(ox); cudaFree(oy); cudaFree(dp);
+    cf_lowess_destroy(h);
+    return rc;
+}
+
+int32_t cf_lowess_smooth(const double* x_sorted, const double* y, int32_t n, double f,
+                         int32_t nsteps, double* ys, double* rw, double* res)
+{
+    if (n < 0 || (n > 0 && (!x_sorted || !y || !ys))) {
+        set_error("Input array sizes must match.");
+        return CF_ARRAY_SIZE_ERROR;
+    }
+    if (nsteps < 0) { set_error("nsteps must be >= 0"); return CF_INVALID_INPUT_ERROR; }
+    cf_lowess* h = nullptr;
+    CF_TRY(cf_lowess_create(&h, -1, nullptr));
+    int rc = cf_lowess_init(h, x_sorted, y, n, 0);
+    if (rc == CF_OK) rc = cf_lowess_run(h, f, nsteps, nullptr);
+    if (rc == CF_OK) {
+        if (n < 2) rc = cf_lowess_fetch(h, ys, nullptr, nullptr);     // rw, res untouched (:651-654)
+        else rc = cf_lowess_fetch(h, ys, nsteps > 0 ? rw : nullptr, res);
+    }
+    cf_lowess_destroy(h);
+    return rc;
+}
+
+int32_t cf_lowess_smooth_batched(const double* x_sorted, const double* y, int32_t nseries,
+                                 int32_t n, double f, int32_t nsteps, double* ys, double* rw,
+                                 double* res)
+{
+    if (nseries < 0 || n < 0) { set_error("Input array sizes must match."); return CF_ARRAY_SIZE_ERROR; }
+    if (nsteps < 0) { set_error("nsteps must be >= 0"); return CF_INVALID_INPUT_ERROR; }
+    if (nseries == 0 || n == 0) return CF_OK;
+    if (!x_sorted || !y || !ys) { set_error("Input array sizes must match."); return CF_ARRAY_SIZE_ERROR; }
+    // independent series: a small pool of handles on their own streams keeps
+    // several series' kernels in flight so that short series still fill the GPU
+    const int pool = nseries < 8 ? nseries : 8;
+    std::vector<cf_lowess*> hs((size_t)pool, nullptr);
+    int rc = CF_OK;
+    for (int k = 0; k < pool && rc == CF_OK; ++k) rc = cf_lowess_create(&hs[(size_t)k], -1, nullptr);
+    auto enqueue = [&](cf_lowess* h, int32_t s) -> int {
+        const size_t off = (size_t)s * (size_t)n, bytes = sizeof(double) * (size_t)n;
+        h->init = false;
+        h->win_f = -1.0;
+        CF_TRY(reserve(h, n));
+        h->n = n;
+        compute_shard(h);
+        CF_TRY(reserve_rw(h));
+        CF_CUDA(cudaMemcpyAsync(h->x, x_sorted + off, bytes, cudaMemcpyHostToDevice, h->stream));
+        CF_CUDA(cudaMemcpyAsync(h->y, y + off, bytes, cudaMemcpyHostToDevice, h->stream));
+        h->init = true;
+        CF_TRY(begin_stage(h, f));
+        if (n < 2) {
+            CF_CUDA(cudaMemcpyAsync(h->ys, h->y, bytes, cudaMemcpyDeviceToDevice, h->stream));
+        } else {
+            bool use_rw = false;
+            for (int32_t p = 0; p <= nsteps; ++p) {
+                CF_TRY(launch_fit(h, use_rw));
+                CF_TRY(launch_residuals(h));
+                if (p < nsteps) { CF_TRY(robust_update(h)); use_rw = true; }
+            }
+        }
+        CF_CUDA(cudaMemcpyAsync(ys + off, h->ys, bytes, cudaMemcpyDeviceToHost, h->stream));
+        if (n >= 2) {
+            if (rw && nsteps > 0) CF_CUDA(cudaMemcpyAsync(rw + off, h->rw, bytes, cudaMemcpyDeviceToHost, h->stream));
+            if (res) CF_CUDA(cudaMemcpyAsync(res + off, h->res, bytes, cudaMemcpyDeviceToHost, h->stream));
+        }
+        return CF_OK;
+    };
+    for (int32_t s = 0; s < nseries && rc == CF_OK; ++s) rc = enqueue(hs[(size_t)(s % pool)], s);
+    for (cf_lowess* h : hs) {
+        if (!h) continue;
+        cudaError_t e = cudaStreamSynchronize(h->stream);
+        if (e != cudaSuccess && rc == CF_OK) rc = cuda_fail(e, "batched smooth", __FILE__, __LINE__);
+        cf_lowess_destroy(h);
+    }
+    return rc;
+}
+
+}  // extern "C"

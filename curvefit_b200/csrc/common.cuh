@@ -1,0 +1,103 @@
+// common.cuh -- internal declarations shared by the libcurvefit_cuda sources.
+// sm_100a only.  Nothing here is part of the public C ABI (include/curvefit_cuda.h).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "curvefit_cuda.h"
+
+namespace cf {
+
+// ---- error plumbing ---------------------------------------------------------
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+
+#define CF_CUDA(call)                                                         \
+    do {                                                                      \
+        cudaError_t e__ = (call);                                             \
+        if (e__ != cudaSuccess)                                               \
+            return ::cf::cuda_fail(e__, #call, __FILE__, __LINE__);           \
+    } while (0)
+
+#define CF_TRY(call)                                                          \
+    do {                                                                      \
+        int rc__ = (call);                                                    \
+        if (rc__ != CF_OK) return rc__;                                       \
+    } while (0)
+
+// ---- select (median of |res|) geometry ---------------------------------------
+// 64-bit keys (bit pattern of |res|, non-negative doubles order as uint64) are
+// resolved most-significant digit first, 11 bits per round, 6 rounds (the last
+// round has 9 live bits).  Two ranks are tracked together: the reference reads
+// rw(m1) and rw(m2), m1 = 1 + n/2, m2 = n - m1 + 1
+// (src/curvefit_regression.f90:699-701).
+constexpr int kSelBits = 11;
+constexpr int kSelBins = 1 << kSelBits;
+constexpr int kSelRounds = 6;
+constexpr int kHistLen = 2 * kSelBins;  // one histogram per tracked rank
+
+struct SelectState {
+    unsigned long long prefix[2];  // resolved high bits of the two order statistics
+    unsigned long long rank[2];    // remaining 0-based rank inside the prefix bucket
+    double cmad, c1, c9;           // :701-703
+};
+
+// ---- per-point neighbourhood (0-based, inclusive) ----------------------------
+struct Windows {
+    int32_t* nleft;   // slide result, :663-669
+    int32_t* lo9;     // first j >= nleft with |x_j - xs| <= .999 h   (:546)
+    int32_t* hi9;     // last  j          with |x_j - xs| <= .999 h
+    int32_t* lo1;     // first j in [lo9,hi9] with |x_j - xs| <= .001 h (w = 1 core)
+    int32_t* hi1;     // last  such j
+    int32_t* leader;  // first index of the tie group of i (:683-689)
+};
+
+}  // namespace cf
+
+// ---- the handle ---------------------------------------------------------------
+struct cf_lowess {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    cudaEvent_t ev[8] = {};
+
+    int32_t n = 0;
+    bool init = false;
+
+    // shard of the sorted index range fitted by this handle
+    int32_t rank = 0, nranks = 1, block = 0, begin = 0, end = 0;
+
+    // device buffers (capacity in elements)
+    int64_t cap = 0, cap_rw = 0;
+    double *x = nullptr, *y = nullptr, *ys = nullptr, *rw = nullptr, *res = nullptr;
+    cf::Windows win = {};
+    double win_f = -1.0;  // span fraction the stored windows were built for
+    int32_t ns = 0;
+
+    unsigned long long* hist = nullptr;  // kHistLen counters
+    cf::SelectState* sel = nullptr;
+
+    // counters for cf_stats
+    int launches = 0, fit_launches = 0;
+};
+
+namespace cf {
+
+// kernels' host launchers (each returns CF_OK or an error code; async on h->stream)
+int launch_windows(cf_lowess* h, int32_t ns);
+int launch_fit(cf_lowess* h, bool use_rw);
+int launch_residuals(cf_lowess* h);           // tie copy + res = y - ys on the shard
+int launch_select_reset(cf_lowess* h);
+int launch_hist(cf_lowess* h, int round);
+int launch_pick(cf_lowess* h, int round);
+int launch_bisquare(cf_lowess* h);
+
+// device radix sort of (x, index) ascending, y co-permuted; d_perm may be null
+int sort_xy_device(const double* d_x_in, const double* d_y_in, int32_t n, double* d_x_out,
+                   double* d_y_out, int32_t* d_perm_out, cudaStream_t s, int* launches);
+
+int fp64_peak(int device, double ms_target, double* tflops, double* mhz);
+
+}  // namespace cf

@@ -1,0 +1,145 @@
+"""One series range-sharded over the GPUs of one box.
+
+One process per GPU (torchrun); every rank holds the whole sorted x, y (16 B
+per point) and the whole robustness-weight vector, fits only its own block
+[begin, end) of output points, and per robustness iteration exchanges
+  * the |res| digit histograms (6 rounds x 4096 uint64 counters, all-reduce)
+    -> every rank resolves the same two order statistics, hence the same cmad
+    (src/curvefit_regression.f90:697-703 -- the reference's full sort);
+  * its block of new robustness weights (all-gather) -- the superset of the
+    (ns-1)-point halo the neighbours need for :551.
+torch.distributed is the plumbing (NCCL on GPUs, gloo in the CPU tests); the
+device stages are libcurvefit_cuda's cf_lowess_stage_* entry points.  Per-point
+sums never cross ranks, so ys is bit-identical for any number of ranks.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import _lib
+
+
+def partition(n: int, nranks: int, tile: int = 512):
+    """Equal blocks of output points, rounded up to the fit kernel's tile so that
+    tile boundaries (and therefore rounding) do not depend on nranks.  Mirrors
+    compute_shard() in csrc/api.cu.  Returns (block, [(begin, end), ...])."""
+    per = -(-n // nranks)
+    per = max(-(-per // tile) * tile, tile)
+    out = []
+    for r in range(nranks):
+        b = min(r * per, n)
+        out.append((b, min(b + per, n)))
+    return per, out
+
+
+class _DevArray:
+    """Zero-copy view of a raw device pointer for torch.as_tensor."""
+
+    def __init__(self, ptr: int, count: int, typestr: str):
+        self.__cuda_array_interface__ = {
+            "shape": (count,), "typestr": typestr, "data": (int(ptr), False), "version": 3,
+            "strides": None,
+        }
+
+
+class DeviceStages:
+    """The CUDA stages of one rank, bound to a lowess_smoothing handle that was
+    created on torch's current stream."""
+
+    def __init__(self, fit, rank: int, nranks: int):
+        self.lib = _lib.load()
+        self.fit = fit
+        self.h = fit._h
+        self.n = fit.get_count()
+        self.rank, self.nranks = rank, nranks
+        self._check(self.lib.cf_lowess_set_shard(self.h, rank, nranks))
+        b, e, blk = C.c_int32(), C.c_int32(), C.c_int32()
+        self.lib.cf_lowess_shard(self.h, C.byref(b), C.byref(e), C.byref(blk))
+        self.begin, self.end, self.block = b.value, e.value, blk.value
+        dev = torch.device("cuda", torch.cuda.current_device())
+        buf = lambda which: self.lib.cf_lowess_buffer(self.h, which)
+        self.hist = torch.as_tensor(_DevArray(buf(_lib.CF_BUF_HIST), self.lib.cf_lowess_hist_len(), "<i8"), device=dev)
+        self.rw = torch.as_tensor(_DevArray(buf(_lib.CF_BUF_RW), nranks * self.block, "<f8"), device=dev)
+        self.ys = torch.as_tensor(_DevArray(buf(_lib.CF_BUF_YS), self.n, "<f8"), device=dev)
+        self.res = torch.as_tensor(_DevArray(buf(_lib.CF_BUF_RES), self.n, "<f8"), device=dev)
+        self.cmad = torch.as_tensor(_DevArray(buf(_lib.CF_BUF_CMAD), 3, "<f8"), device=dev)
+        self.rounds = self.lib.cf_lowess_select_rounds()
+        self.launches = 0
+
+    def _check(self, rc: int) -> None:
+        if rc != 0:
+            raise RuntimeError(f"libcurvefit_cuda stage failed ({rc}): {_lib.last_error()}")
+
+    def begin_run(self, f: float) -> None:
+        self._check(self.lib.cf_lowess_stage_begin(self.h, float(f)))
+
+    def fit_pass(self, use_rw: bool) -> None:
+        self._check(self.lib.cf_lowess_stage_fit(self.h, 1 if use_rw else 0))
+
+    def hist_round(self, r: int) -> None:
+        self._check(self.lib.cf_lowess_stage_hist(self.h, r))
+
+    def pick_round(self, r: int) -> None:
+        self._check(self.lib.cf_lowess_stage_pick(self.h, r))
+
+    def weights(self) -> None:
+        self._check(self.lib.cf_lowess_stage_weights(self.h))
+
+    def sync(self) -> None:
+        self._check(self.lib.cf_lowess_sync(self.h))
+
+
+class ShardedLowess:
+    """lowess() over `stages.nranks` ranks.  `stages` is DeviceStages on GPUs; the
+    CPU tests pass a stand-in with the same attributes to exercise this host
+    logic over gloo."""
+
+    def __init__(self, stages, group: Optional[dist.ProcessGroup] = None):
+        self.s = stages
+        self.group = group
+        self.collectives = 0
+
+    def run(self, f: float, nsteps: int = 2, gather: bool = True):
+        s = self.s
+        multi = s.nranks > 1
+        s.begin_run(f)
+        for p in range(nsteps + 1):                           # :657
+            s.fit_pass(p > 0)                                 # :662-695 on the block
+            if p == nsteps:                                   # :696
+                break
+            for r in range(s.rounds):                         # :697-703 as a radix select
+                s.hist_round(r)
+                if multi:
+                    dist.all_reduce(s.hist, op=dist.ReduceOp.SUM, group=self.group)
+                    self.collectives += 1
+                s.pick_round(r)
+            s.weights()                                       # :704-713 on the block
+            if multi:
+                own = s.rw[s.rank * s.block:(s.rank + 1) * s.block]
+                dist.all_gather_into_tensor(s.rw, own, group=self.group)
+                self.collectives += 1
+        if not gather:
+            return None
+        return self.gather_results()
+
+    def gather_results(self):
+        """Full-length ys and res on every rank (block-padded all-gather)."""
+        s = self.s
+        if s.nranks == 1:
+            return s.ys[: s.n], s.res[: s.n]
+        outs = []
+        for src in (s.ys, s.res):
+            own = torch.zeros(s.block, dtype=src.dtype, device=src.device)
+            cnt = s.end - s.begin
+            if cnt > 0:
+                own[:cnt] = src[s.begin:s.end]
+            full = torch.empty(s.nranks * s.block, dtype=src.dtype, device=src.device)
+            dist.all_gather_into_tensor(full, own, group=self.group)
+            self.collectives += 1
+            outs.append(full[: s.n])
+        return outs[0], outs[1]

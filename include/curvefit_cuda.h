@@ -1,0 +1,183 @@
+/*
+ * curvefit_cuda.h -- C ABI of libcurvefit_cuda (sm_100a only, no CPU fallback).
+ *
+ * Drop-in boundary for ONE path of jchristopherson/curvefit: robust LOWESS
+ * smoothing, i.e. lowess_smoothing%initialize / %smooth
+ * (src/curvefit_regression.f90:218-247 type, :740-811 ls_init, :832-868
+ * ls_smooth, :625-715 lowess, :513-586 lowest).  The reference has no FFI layer
+ * for this path (its only C interop is FERROR's, ferror.h); these entry points
+ * are what a `bind(C)` interface block in curvefit_regression.f90 would bind
+ * (see fortran/curvefit_regression_cuda.f90 and INTEGRATION.md).
+ *
+ * Conventions
+ *  - plain pointers and sizes, no C++/torch types; all arrays real64 / int32
+ *    like the reference (real(real64), integer(int32));
+ *  - every function returns 0 on success, else one of the CF_* codes below (the
+ *    reference's own values) -- it never exits, prints or throws;
+ *    cf_last_error() gives a thread-local detail string;
+ *  - "host" pointers are caller-owned and never retained past the call;
+ *  - indices written to int32 outputs are 1-BASED like the reference's
+ *    nleft/nright (src/curvefit_regression.f90:658-669);
+ *  - one handle must not be used from two threads at once (the reference's
+ *    object is intent(inout) in smooth, :834); distinct handles are independent.
+ */
+#ifndef CURVEFIT_CUDA_H_
+#define CURVEFIT_CUDA_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define CF_API __declspec(dllexport)
+#else
+#define CF_API __attribute__((visibility("default")))
+#endif
+
+/* Error codes.  202/105/300/201 are the reference's (src/curvefit_core.f90:34-40
+ * via nonlin_constants.f90:18,20 and linalg_constants.f90:23); 303 is new
+ * (300-302 are taken, curvefit_core.f90:38,43,54) and means a CUDA failure. */
+#define CF_OK 0
+#define CF_OUT_OF_MEMORY_ERROR 105
+#define CF_INVALID_INPUT_ERROR 201
+#define CF_ARRAY_SIZE_ERROR 202
+#define CF_NO_DATA_DEFINED_ERROR 300
+#define CF_DEVICE_ERROR 303
+
+/* Library version (major*10000 + minor*100 + patch). */
+CF_API int32_t cf_version(void);
+
+/* Copies the calling thread's last error detail (NUL terminated) into buf;
+ * returns the length that was needed. */
+CF_API int32_t cf_last_error(char* buf, int32_t len);
+
+/* Span of the local fit: ns = max(min(int(f*n), n), 2)
+ * -- src/curvefit_regression.f90:647 (truncation, not ceil). */
+CF_API int32_t cf_lowess_span(int32_t n, double f);
+
+/* ------------------------------------------------------------------------
+ * Stateless entry points (HOST buffers) -- what the Fortran shim calls.
+ * ---------------------------------------------------------------------- */
+
+/* ls_init with srt=.true., data part (src/curvefit_regression.f90:791-799):
+ * x_sorted = ascending x, y_sorted = y co-permuted.  Replaces
+ * sort(m_x, indices, .true.) (LINALG linalg_sorting.f90:38-78, 277-354) with a
+ * stable device LSD radix sort; `perm` (may be NULL) receives the 1-based
+ * tracking indices.  In/out arrays may not alias. */
+CF_API int32_t cf_sort_xy(const double* x, const double* y, int32_t n,
+                          double* x_sorted, double* y_sorted, int32_t* perm);
+
+/* lowess(x, y, f, nsteps, delta=0, ys, rw, res)
+ * (src/curvefit_regression.f90:625-715, as called from ls_smooth :866 with
+ * nsteps = 2).  x ascending, all arrays length n.  n < 2: ys = y, rw/res
+ * untouched (:651-654).  nsteps = 0: rw untouched (never written, :696). */
+CF_API int32_t cf_lowess_smooth(const double* x_sorted, const double* y, int32_t n,
+                                double f, int32_t nsteps,
+                                double* ys, double* rw, double* res);
+
+/* nseries independent series, row-major [nseries][n]; same semantics per row. */
+CF_API int32_t cf_lowess_smooth_batched(const double* x_sorted, const double* y,
+                                        int32_t nseries, int32_t n, double f,
+                                        int32_t nsteps,
+                                        double* ys, double* rw, double* res);
+
+/* ------------------------------------------------------------------------
+ * Device-resident handle -- the lowess_smoothing object's state on one GPU
+ * (m_x, m_y, m_weights, m_residuals: src/curvefit_regression.f90:218-233).
+ * ---------------------------------------------------------------------- */
+typedef struct cf_lowess cf_lowess;
+
+typedef struct cf_stats {
+    float ms_total;      /* whole run, CUDA events on the handle's stream     */
+    float ms_windows;    /* neighbourhood search                              */
+    float ms_fit;        /* sum over passes of the local-fit kernel           */
+    float ms_robust;     /* residuals + select + bisquare, summed over passes */
+    int32_t fit_launches;
+    int32_t launches;    /* all kernels of this library launched by the run   */
+    int32_t ns;          /* span used                                         */
+    int32_t passes;      /* nsteps + 1                                        */
+    double cmad_last;    /* cmad of the last robustness iteration (:701)      */
+} cf_stats;
+
+/* device < 0: current device.  stream: a cudaStream_t (as void*) or NULL for a
+ * private non-blocking stream owned by the handle. */
+CF_API int32_t cf_lowess_create(cf_lowess** h, int32_t device, void* stream);
+CF_API void cf_lowess_destroy(cf_lowess* h);
+
+/* ls_init (src/curvefit_regression.f90:740-811): copy host x, y to the device;
+ * sort != 0 sorts x ascending and co-permutes y (default of the reference).
+ * No monotonicity check when sort == 0, like the reference (:800-803). */
+CF_API int32_t cf_lowess_init(cf_lowess* h, const double* x, const double* y,
+                              int32_t n, int32_t sort);
+/* Same, x and y already in device memory (device-to-device copy). */
+CF_API int32_t cf_lowess_init_device(cf_lowess* h, const void* d_x, const void* d_y,
+                                     int32_t n, int32_t sort);
+
+/* Restrict the fitted output points to block `rank` of `nranks` equal blocks
+ * of the sorted index range (multi-GPU range partition).  Default 0 of 1. */
+CF_API int32_t cf_lowess_set_shard(cf_lowess* h, int32_t rank, int32_t nranks);
+CF_API int32_t cf_lowess_shard(const cf_lowess* h, int32_t* begin, int32_t* end,
+                               int32_t* block);
+
+/* ls_smooth's work on the device (lowess, :625-715), nsteps robustness
+ * iterations, whole series on this GPU.  Synchronous.  stats may be NULL. */
+CF_API int32_t cf_lowess_run(cf_lowess* h, double f, int32_t nsteps, cf_stats* stats);
+
+/* Teacher forcing: `passes` fit passes starting from the given robustness
+ * weights (host, length n; NULL = first pass without weights). */
+CF_API int32_t cf_lowess_run_from_rw(cf_lowess* h, double f, const double* rw_in,
+                                     int32_t passes);
+
+/* Copy results to host buffers (each may be NULL): last ys, m_weights,
+ * m_residuals (what get_residuals returns, :928-939). */
+CF_API int32_t cf_lowess_fetch(cf_lowess* h, double* ys, double* rw, double* res);
+/* Sorted x / y (what get_x / get_y index, :893-920). */
+CF_API int32_t cf_lowess_fetch_xy(cf_lowess* h, double* x_sorted, double* y_sorted);
+CF_API int32_t cf_lowess_count(const cf_lowess* h);  /* get_count, :876-884 */
+
+/* Neighbourhoods for span fraction f, 1-based, each array length n or NULL:
+ * nleft/nright as the slide loop leaves them (:663-669); lo9/hi9 = first/last
+ * index with a non-zero tricube weight (r <= .999h, :546); lo1/hi1 = the
+ * w = 1 core (r <= .001h, :547-551); leader = index of the first member of the
+ * point's tie group (:683-689; followers copy its ys). */
+CF_API int32_t cf_lowess_windows(cf_lowess* h, double f,
+                                 int32_t* nleft, int32_t* nright,
+                                 int32_t* lo9, int32_t* hi9,
+                                 int32_t* lo1, int32_t* hi1, int32_t* leader);
+
+/* ------------------------------------------------------------------------
+ * Stage API -- the same device stages cf_lowess_run chains, exposed so that a
+ * multi-GPU driver (one process per GPU) can put its collectives between
+ * them.  All stages are asynchronous on the handle's stream.
+ * ---------------------------------------------------------------------- */
+CF_API int32_t cf_lowess_stage_begin(cf_lowess* h, double f);        /* windows          */
+CF_API int32_t cf_lowess_stage_fit(cf_lowess* h, int32_t use_rw);    /* fit + res, shard */
+CF_API int32_t cf_lowess_stage_hist(cf_lowess* h, int32_t round);    /* |res| digit hist */
+CF_API int32_t cf_lowess_stage_pick(cf_lowess* h, int32_t round);    /* scan (post-sum)  */
+CF_API int32_t cf_lowess_stage_weights(cf_lowess* h);                /* bisquare, shard  */
+CF_API int32_t cf_lowess_select_rounds(void);
+CF_API int32_t cf_lowess_sync(cf_lowess* h);
+
+/* Device pointers of the handle's buffers, for zero-copy wrapping by the host
+ * runtime (e.g. as torch tensors for NCCL collectives). */
+#define CF_BUF_X 0
+#define CF_BUF_Y 1
+#define CF_BUF_YS 2
+#define CF_BUF_RW 3      /* length = nranks * block (padded for all-gather)  */
+#define CF_BUF_RES 4
+#define CF_BUF_HIST 5    /* uint64 counters, cf_lowess_hist_len() of them     */
+#define CF_BUF_CMAD 6    /* double[3]: cmad, c1, c9 of the last iteration     */
+CF_API void* cf_lowess_buffer(cf_lowess* h, int32_t which);
+CF_API int32_t cf_lowess_hist_len(void);
+
+/* FP64 pipe peak microbenchmark (independent DFMA chains on every SM):
+ * returns measured TFLOP/s (FMA = 2 flop) over `ms_target` milliseconds. */
+CF_API int32_t cf_fp64_peak(int32_t device, double ms_target, double* tflops,
+                            double* sm_mhz_est);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CURVEFIT_CUDA_H_ */

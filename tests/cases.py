@@ -1,0 +1,43 @@
+"""Seeded input families shared by the CPU and GPU parity tests."""
+import numpy as np
+
+from curvefit_b200 import datagen
+
+
+def make_x(kind: str, n: int, seed: int = 0) -> np.ndarray:
+    rng = np.random.default_rng(1234 + seed)
+    if kind == "grid":
+        return datagen.grid_x(n)
+    if kind == "uniform":
+        return np.sort(datagen.random_x(n, seed))
+    if kind == "clustered":
+        c = rng.normal(size=n) * 0.02 + rng.integers(0, 4, size=n) * 0.3
+        return np.sort(c)
+    if kind == "ties":
+        return np.sort(np.round(rng.random(n) * max(n // 8, 2)) / max(n // 8, 2))
+    if kind == "equal":
+        return np.full(n, 0.75)
+    if kind == "wide":
+        return np.sort(np.exp(rng.normal(size=n) * 3.0))
+    raise ValueError(kind)
+
+
+def make_y(x: np.ndarray, seed: int = 0, outliers: bool = True) -> np.ndarray:
+    y = datagen.noisy_y(x, seed)
+    if outliers and x.size >= 20:
+        rng = np.random.default_rng(99 + seed)
+        k = rng.choice(x.size, size=max(x.size // 50, 1), replace=False)
+        y[k] += rng.choice([-8.0, 8.0], size=k.size)
+    return y
+
+
+def close(a, b, tol=1e-10):
+    """|d_i| <= tol * max(|ref_i|, 1e-3 * max|ref|) and normwise tol."""
+    a = np.asarray(a)
+    b = np.asarray(b)
+    scale = np.max(np.abs(b)) if b.size else 0.0
+    floor = np.maximum(np.abs(b), 1e-3 * scale)
+    d = np.abs(a - b)
+    point = bool(np.all(d <= tol * floor + 1e-300))
+    norm = bool(d.max(initial=0.0) <= tol * scale + 1e-300)
+    return point and norm, float(d.max(initial=0.0))

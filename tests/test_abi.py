@@ -1,0 +1,98 @@
+"""CPU tests of the drop-in boundary: the C-ABI library loads, exports every
+symbol include/curvefit_cuda.h declares, and fails LOUDLY without a GPU (no
+CPU fallback).  No device compute here."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from curvefit_b200 import _lib, core
+from curvefit_b200.errors import errors
+from curvefit_b200.regression import lowess_smoothing
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    text = open(os.path.join(ROOT, "include", "curvefit_cuda.h")).read()
+    return sorted(set(re.findall(r"CF_API\s+[\w\s\*]+?\b(cf_\w+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = _lib.load()
+    names = _declared_symbols()
+    assert len(names) >= 25
+    for name in names:
+        assert hasattr(lib, name), name
+    assert set(names) == set(_lib.SIGNATURES), set(names) ^ set(_lib.SIGNATURES)
+    assert lib.cf_version() >= 100
+
+
+def test_span_matches_reference_truncation():
+    lib = _lib.load()
+    assert lib.cf_lowess_span(16384, 0.3) == 4915        # F3: trunc, not ceil
+    assert lib.cf_lowess_span(100000000, 0.05) == 5000000
+    assert lib.cf_lowess_span(100, 0.2) == 20
+    assert lib.cf_lowess_span(100, 0.0) == 2
+    assert lib.cf_lowess_span(100, 7.0) == 100
+
+
+def test_error_codes_are_the_references():
+    # /root/reference src/curvefit_core.f90:34-40
+    assert (core.CF_ARRAY_SIZE_ERROR, core.CF_OUT_OF_MEMORY_ERROR,
+            core.CF_NO_DATA_DEFINED_ERROR, core.CF_INVALID_INPUT_ERROR) == (202, 105, 300, 201)
+    hdr = open(os.path.join(ROOT, "include", "curvefit_cuda.h")).read()
+    for name, val in (("CF_ARRAY_SIZE_ERROR", 202), ("CF_OUT_OF_MEMORY_ERROR", 105),
+                      ("CF_NO_DATA_DEFINED_ERROR", 300), ("CF_INVALID_INPUT_ERROR", 201),
+                      ("CF_DEVICE_ERROR", 303)):
+        assert re.search(rf"#define\s+{name}\s+{val}\b", hdr), name
+
+
+def _have_gpu():
+    try:
+        import torch
+        return torch.cuda.is_available()
+    except Exception:
+        return False
+
+
+@pytest.mark.skipif(_have_gpu(), reason="checks the no-GPU failure mode")
+def test_no_cpu_fallback_without_a_device():
+    lib = _lib.load()
+    h = C.c_void_p()
+    assert lib.cf_lowess_create(C.byref(h), -1, None) == core.CF_DEVICE_ERROR
+    assert "no CPU fallback" in _lib.last_error() or "CUDA" in _lib.last_error()
+    x = np.linspace(0, 1, 10)
+    ys = np.zeros(10)
+    rc = lib.cf_lowess_smooth(x.ctypes.data_as(_lib.c_dp), x.ctypes.data_as(_lib.c_dp), 10, 0.5, 2,
+                              ys.ctypes.data_as(_lib.c_dp), ys.ctypes.data_as(_lib.c_dp),
+                              ys.ctypes.data_as(_lib.c_dp))
+    assert rc == core.CF_DEVICE_ERROR
+    fit = lowess_smoothing()
+    with pytest.raises(core.CurvefitError) as ei:
+        fit.initialize(x, x)
+    assert ei.value.flag == core.CF_DEVICE_ERROR and ei.value.fcn == "ls_init"
+
+
+def test_host_side_error_behaviour_mirrors_reference():
+    """ls_init size check (:769-773) and ls_smooth's m_init guard (:850-855) with
+    a caller-supplied error object that does not terminate."""
+    fit = lowess_smoothing()
+    err = errors()
+    err.set_exit_on_error(False)
+    err.set_suppress_printing(True)
+    fit.initialize(np.zeros(5), np.zeros(4), err=err)
+    assert err.has_error_occurred() and err.get_error_flag() == 202
+    assert err.get_error_fcn_name() == "ls_init"
+    assert err.get_error_message() == "Input array sizes must match."
+    assert fit.get_count() == 0 and fit.get_x(1) == 0.0 and fit.get_y(3) == 0.0
+    err.reset_error_status()
+    assert fit.smooth(0.5, err=err) is None
+    assert err.get_error_flag() == 300 and err.get_error_fcn_name() == "ls_smooth"
+    assert err.get_error_message() == "No data has been defined."
+    # default error object "terminates": here it raises
+    with pytest.raises(core.CurvefitError) as ei:
+        lowess_smoothing().smooth(0.5)
+    assert ei.value.flag == 300
