@@ -5,6 +5,7 @@
 // a CUDA device and reports CF_DEVICE_ERROR otherwise.
 #include <math.h>
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <new>
@@ -173,6 +174,8 @@ int32_t cf_lowess_create(cf_lowess** out, int32_t device, void* stream)
     cf_lowess* h = new (std::nothrow) cf_lowess();
     if (!h) { set_error("Insufficient memory available."); return CF_OUT_OF_MEMORY_ERROR; }
     h->device = device;
+    if (const char* v = getenv("CF_FIT_VARIANT")) h->fit_variant = atoi(v);
+    if (const char* v = getenv("CF_FIT_KSPLIT")) h->ksplit_override = atoi(v);
     if (stream) {
         h->stream = (cudaStream_t)stream;
     } else {
@@ -201,6 +204,7 @@ void cf_lowess_destroy(cf_lowess* h)
     free_buffers(h);
     cudaFree(h->hist);
     cudaFree(h->sel);
+    cudaFree(h->part);
     for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
     delete h;

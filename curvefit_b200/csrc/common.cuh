@@ -79,6 +79,13 @@ struct cf_lowess {
     unsigned long long* hist = nullptr;  // kHistLen counters
     cf::SelectState* sel = nullptr;
 
+    // fit kernel: partial-moment scratch for the K-way window split, tuning knobs
+    double* part = nullptr;
+    size_t part_bytes = 0;
+    int sms = 0;
+    int fit_variant = 0;       // env CF_FIT_VARIANT (development only)
+    int ksplit_override = 0;   // env CF_FIT_KSPLIT  (development only)
+
     // counters for cf_stats
     int launches = 0, fit_launches = 0;
 };

@@ -2,25 +2,32 @@
 // points (src/curvefit_regression.f90:513-586 as called from
 // :671-673).  This kernel is > 99.9 % of smooth() and is FP64-pipe bound.
 //
-// Decomposition.  A CTA owns a tile of T = NT*P consecutive output points
-// (P per thread, kept in registers) and streams the union of their windows
-// through shared memory in double-buffered chunks of C elements.  Every window
-// element is read by all threads as a shared-memory BROADCAST, so there is no
-// reduction and each point's sums run over ascending j like the reference.
+// Decomposition.  A tile is T = NT*P consecutive output points (P per thread,
+// accumulators in registers).  A CTA streams (a K-th part of) the union of the
+// tile's windows through shared memory in double-buffered chunks of C elements;
+// every window element is read by all threads as a shared-memory BROADCAST, so
+// there is no reduction and each point's sums run over ascending j like the
+// reference.  When the tile count does not fill the GPU evenly, every tile's
+// window is cut into K parts handled by K CTAs (partial moments to scratch,
+// combined in part order by fit_finalize_kernel), so the grid is many waves
+// deep and the tail is short.
 //
 // Arithmetic.  The reference makes 5-6 dependent sweeps (weights, normalise,
 // mean, variance, reweight, dot with y).  They collapse into one sweep over
 // five moments of the tricube x robustness weights:
 //     S0 = sum w      S1 = sum w u      S2 = sum w u^2
-//     T0 = sum w y    T1 = sum w u y          u_j = (x_j - xc) / hc
-// with (xc, hc) a per-CTA centre/scale, so the factors that depend only on j
-//     rw, rw u, rw u^2, rw y, rw u y
-// are formed ONCE per chunk while staging and every (point, element) pair costs
-// 10 FP64-pipe instructions: q = fma(u, a_p, b_p) (= (x_j - xs)/h), q^2,
-// t = 1 - q^2|q|, t^2, t^3, and five FMAs.  The three-way decisions of the
-// reference (r <= h1 -> w = 1, r > h9 -> w = 0, sweep exit) are taken from the
-// integer ranges produced by windows.cu, never from the rounded q, so the set
-// of contributing elements is exactly the reference's.
+//     T0 = sum w y    T1 = sum w u y
+// FAST path: u_j = (x_j - xc)/hc with a per-tile centre/scale, so the factors
+// that depend only on j (rw, rw u, rw u^2, rw y, rw u y) are formed ONCE per
+// chunk while staging and every (point, element) pair costs 10 FP64-pipe
+// instructions: q = fma(u, a_p, b_p) (= (x_j - xs)/h), q^2, t = 1 - q^2|q|,
+// t^2, t^3, five FMAs.  EXACT path (tiles whose bandwidths vary so much that a
+// shared centre/scale would lose digits: window width / min h > 16): u = q is
+// formed per point from d = x_j - xs exactly as the reference forms r, 13
+// instructions per pair.  The three-way decisions of the reference (r <= h1 ->
+// w = 1, r > h9 -> w = 0, sweep exit) are taken from the integer ranges of
+// windows.cu, never from the rounded q, so the set of contributing elements is
+// exactly the reference's.
 #include "common.cuh"
 
 namespace cf {
@@ -30,9 +37,12 @@ struct FitParams {
     const double* y;
     const double* rw;   // nullptr on the first pass (userw = .false., :671)
     double* ys;
+    double* part;       // [tile][K][5][T] partial moments when K > 1
     Windows w;
-    int32_t n, ns, begin, end;
+    int32_t n, ns, begin, end, ksplit;
 };
+
+constexpr double kExactRatio = 16.0;
 
 __device__ __forceinline__ int warp_min(int v)
 {
@@ -52,36 +62,50 @@ __device__ __forceinline__ double warp_maxd(double v)
     for (int o = 16; o; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
     return v;
 }
-
-template <int NT, int P, int E>
-__global__ void __launch_bounds__(NT)
-fit_kernel(const FitParams prm)
+__device__ __forceinline__ double warp_mind(double v)
 {
-    constexpr int C = NT * E;      // window elements per staged chunk
-    constexpr int T = NT * P;      // output points per CTA
-    constexpr int NW = NT / 32;
+#pragma unroll
+    for (int o = 16; o; o >>= 1) v = fmin(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
 
-    __shared__ double2 sm[2][3][C];
-    __shared__ int s_lo[NW], s_hi[NW];
-    __shared__ double s_h[NW];
+// Tile-level facts shared by the fit and finalize kernels.
+template <int NT, int P>
+struct Tile {
+    static constexpr int T = NT * P;
+    static constexpr int NW = NT / 32;
+    // per thread
+    bool valid[P];
+    double hp[P], xsp[P];
+    // per warp
+    int wlo, whi, flo, fhi, clo, chi;
+    // per CTA
+    int jlo, jhi;
+    double xc, hc, sc;
+    bool exact;
+};
 
+struct TileShared {
+    int lo[8], hi[8];
+    double hmax[8], hmin[8];
+};
+
+// Reads the windows of the tile's points, publishes the per-point integer ranges
+// to shared memory (rng[4][T]) and reduces the tile-level quantities.
+template <int NT, int P>
+__device__ __forceinline__ void tile_setup(const FitParams& prm, int32_t tile0, Tile<NT, P>& t,
+                                           int32_t (*rng)[NT * P], TileShared& ts)
+{
+    constexpr int T = NT * P, NW = NT / 32;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int32_t tile0 = prm.begin + (int32_t)blockIdx.x * T;
     const int32_t tile_end = min(tile0 + T, prm.end);
     const double* __restrict__ x = prm.x;
-    const double* __restrict__ y = prm.y;
-    const double* __restrict__ rw = prm.rw;
-
-    // ---- per-point setup -----------------------------------------------------
-    int32_t pi[P], lo9[P], hi9[P], lo1[P], hi1[P];
-    double hp[P], xsp[P];
-    bool valid[P];
     int wlo = INT32_MAX, whi = -1, flo = -1, fhi = INT32_MAX, clo = INT32_MAX, chi = -1;
-    double hmax = 0.0;
+    double hmax = 0.0, hmin = 1.7976931348623157e308;
 #pragma unroll
     for (int p = 0; p < P; ++p) {
-        const int32_t i = tile0 + wid * (32 * P) + p * 32 + lane;
-        pi[p] = i;
+        const int loc = wid * (32 * P) + p * 32 + lane;
+        const int32_t i = tile0 + loc;
         // tie followers copy their leader's value later (robust.cu); a shard that
         // starts inside a tie group fits its first point in the leader's place
         bool v = i < tile_end;
@@ -89,49 +113,110 @@ fit_kernel(const FitParams prm)
             const int32_t l = prm.w.leader[i];
             v = (l == i) || (i == prm.begin && l < i);
         }
-        valid[p] = v;
-        if (valid[p]) {
+        t.valid[p] = v;
+        int l9 = 1, r9 = 0, l1 = 1, r1 = 0;       // empty ranges for idle slots
+        if (v) {
             const int32_t nl = prm.w.nleft[i];
             const double xs = x[i];
             const double hl = xs - x[nl], hr = x[nl + prm.ns - 1] - xs;   // :536
-            hp[p] = hl > hr ? hl : hr;
-            xsp[p] = xs;
-            lo9[p] = prm.w.lo9[i]; hi9[p] = prm.w.hi9[i];
-            lo1[p] = prm.w.lo1[i]; hi1[p] = prm.w.hi1[i];
-            wlo = min(wlo, lo9[p]); whi = max(whi, hi9[p]);
-            clo = min(clo, lo1[p]); chi = max(chi, hi1[p]);
-            flo = max(flo, lo9[p]); fhi = min(fhi, hi9[p]);
-            hmax = fmax(hmax, hp[p]);
+            const double h = hl > hr ? hl : hr;
+            t.hp[p] = h;
+            t.xsp[p] = xs;
+            l9 = prm.w.lo9[i]; r9 = prm.w.hi9[i];
+            l1 = prm.w.lo1[i]; r1 = prm.w.hi1[i];
+            wlo = min(wlo, l9); whi = max(whi, r9);
+            clo = min(clo, l1); chi = max(chi, r1);
+            flo = max(flo, l9); fhi = min(fhi, r9);
+            hmax = fmax(hmax, h);
+            if (h > 0.0) hmin = fmin(hmin, h);
         } else {
-            hp[p] = 0.0; xsp[p] = 0.0;
-            lo9[p] = 1; hi9[p] = 0; lo1[p] = 1; hi1[p] = 0;   // empty ranges
-            flo = INT32_MAX; fhi = -1;                        // no fast chunks
+            t.hp[p] = 0.0; t.xsp[p] = 0.0;
+            flo = INT32_MAX; fhi = -1;                // no fast chunks for this warp
         }
+        rng[0][loc] = l9; rng[1][loc] = r9; rng[2][loc] = l1; rng[3][loc] = r1;
     }
-    wlo = warp_min(wlo); whi = warp_max(whi);
-    flo = warp_max(flo); fhi = warp_min(fhi);
-    clo = warp_min(clo); chi = warp_max(chi);
-    hmax = warp_maxd(hmax);
-    if (lane == 0) { s_lo[wid] = wlo; s_hi[wid] = whi; s_h[wid] = hmax; }
+    t.wlo = warp_min(wlo); t.whi = warp_max(whi);
+    t.flo = warp_max(flo); t.fhi = warp_min(fhi);
+    t.clo = warp_min(clo); t.chi = warp_max(chi);
+    hmax = warp_maxd(hmax); hmin = warp_mind(hmin);
+    if (lane == 0) { ts.lo[wid] = t.wlo; ts.hi[wid] = t.whi; ts.hmax[wid] = hmax; ts.hmin[wid] = hmin; }
     __syncthreads();
     int jlo = INT32_MAX, jhi = -1;
-    double hc = 0.0;
+    double hc = 0.0, hm = 1.7976931348623157e308;
 #pragma unroll
     for (int w = 0; w < NW; ++w) {
-        jlo = min(jlo, s_lo[w]); jhi = max(jhi, s_hi[w]); hc = fmax(hc, s_h[w]);
+        jlo = min(jlo, ts.lo[w]); jhi = max(jhi, ts.hi[w]);
+        hc = fmax(hc, ts.hmax[w]); hm = fmin(hm, ts.hmin[w]);
     }
-    if (jlo > jhi) return;                     // tile holds tie followers only
+    t.jlo = jlo; t.jhi = jhi;
+    t.exact = false;
+    if (jlo <= jhi) {
+        // a shared centre/scale loses digits when some bandwidth is tiny next to
+        // the width of the tile's window union
+        const double width = x[jhi] - x[jlo];
+        t.exact = hc > 0.0 && !(width <= kExactRatio * hm);
+    }
     if (!(hc > 0.0)) hc = 1.0;
-    const double sc = 1.0 / hc;
-    const double xc = x[min(tile0 + T / 2, prm.n - 1)];
+    t.hc = hc;
+    t.sc = 1.0 / hc;
+    t.xc = x[min(tile0 + T / 2, prm.n - 1)];
+}
 
+// local linear fit evaluated at xs from the five moments (:559-584)
+__device__ __forceinline__ double fit_value(double S0, double S1, double S2, double T0, double T1,
+                                            double yi, double h, double scale, double us,
+                                            double range)
+{
+    if (!(S0 > 0.0)) return yi;                       // ok = .false., :559, :673
+    const double inv = 1.0 / S0;
+    const double ym = T0 * inv;                       // weighted mean of y
+    double out = ym;
+    if (h > 0.0) {                                    // :564
+        const double um = S1 * inv;
+        double cu = fma(-um, um, S2 * inv);           // weighted variance of u
+        cu = cu > 0.0 ? cu : 0.0;
+        if (sqrt(cu) * scale > 0.001 * range) {       // :573 (c = cu * scale^2)
+            const double cov = fma(-um, ym, T1 * inv);
+            out = fma(cov / cu, us - um, ym);
+        }
+    }
+    return out;
+}
+
+template <int NT, int P, int E, int MINB>
+__global__ void __launch_bounds__(NT, MINB)
+fit_kernel(const FitParams prm)
+{
+    constexpr int C = NT * E;      // window elements per staged chunk
+    constexpr int T = NT * P;      // output points per tile
+
+    __shared__ double2 sm[2][3][C];
+    __shared__ int32_t rng[4][T];
+    __shared__ TileShared ts;
+
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int K = prm.ksplit;
+    const int tile = blockIdx.x / K, part = blockIdx.x - tile * K;
+    const int32_t tile0 = prm.begin + (int32_t)tile * T;
+    const double* __restrict__ x = prm.x;
+    const double* __restrict__ y = prm.y;
+    const double* __restrict__ rw = prm.rw;
+
+    Tile<NT, P> t;
+    tile_setup<NT, P>(prm, tile0, t, rng, ts);
+    const int jlo = t.jlo, jhi = t.jhi;
+    if (jlo > jhi) return;                     // tile holds tie followers only
+    const double xc = t.xc, sc = t.sc;
+    const bool exact = t.exact;
+
+    // per-point constants: fast q = fma(u, ap, bp); exact q = (x_j - bp) * ap
     double ap[P], bp[P];
     double S0[P], S1[P], S2[P], T0[P], T1[P];
 #pragma unroll
     for (int p = 0; p < P; ++p) {
-        const double invh = hp[p] > 0.0 ? 1.0 / hp[p] : 0.0;
-        ap[p] = hc * invh;
-        bp[p] = (xc - xsp[p]) * invh;
+        const double invh = t.hp[p] > 0.0 ? 1.0 / t.hp[p] : 0.0;
+        ap[p] = exact ? invh : t.hc * invh;
+        bp[p] = exact ? t.xsp[p] : (xc - t.xsp[p]) * invh;
         S0[p] = S1[p] = S2[p] = T0[p] = T1[p] = 0.0;
     }
 
@@ -151,32 +236,68 @@ fit_kernel(const FitParams prm)
 #pragma unroll
         for (int e = 0; e < E; ++e) {
             const int k = e * NT + tid;
-            const double u = (rx[e] - xc) * sc;
-            const double ru = rr[e] * u, ryy = rr[e] * ry[e];
-            sm[buf][0][k] = make_double2(u, rr[e]);
-            sm[buf][1][k] = make_double2(ru, ru * u);
-            sm[buf][2][k] = make_double2(ryy, ryy * u);
+            if (exact) {
+                sm[buf][0][k] = make_double2(rx[e], rr[e]);
+                sm[buf][1][k] = make_double2(ry[e], 0.0);
+            } else {
+                const double u = (rx[e] - xc) * sc;
+                const double ru = rr[e] * u, ryy = rr[e] * ry[e];
+                sm[buf][0][k] = make_double2(u, rr[e]);
+                sm[buf][1][k] = make_double2(ru, ru * u);
+                sm[buf][2][k] = make_double2(ryy, ryy * u);
+            }
         }
     };
 
-    const int nchunks = (jhi - jlo) / C + 1;
-    fetch(jlo);
-    stash(0);
+    const int nch = (jhi - jlo) / C + 1;
+    const int k0 = (int)(((long long)nch * part) / K);
+    const int k1 = (int)(((long long)nch * (part + 1)) / K);
+    if (k0 < k1) {
+        fetch(jlo + k0 * C);
+        stash(k0 & 1);
+    }
     __syncthreads();
 
-    for (int kc = 0; kc < nchunks; ++kc) {
+    for (int kc = k0; kc < k1; ++kc) {
         const int32_t c = jlo + kc * C, cend = c + C - 1;
         const int buf = kc & 1;
-        const bool more = kc + 1 < nchunks;
+        const bool more = kc + 1 < k1;
         if (more) fetch(c + C);
 
         const double2* __restrict__ p0 = sm[buf][0];
         const double2* __restrict__ p1 = sm[buf][1];
         const double2* __restrict__ p2 = sm[buf][2];
 
-        if (cend < wlo || c > whi) {
+        if (cend < t.wlo || c > t.whi) {
             // nothing for this warp in the chunk
-        } else if (c >= flo && cend <= fhi && (cend < clo || c > chi)) {
+        } else if (exact) {
+            // per-point centring, 13 FP64 instructions per pair, integer range tests
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                const int loc = wid * (32 * P) + p * 32 + lane;
+                const int l9 = rng[0][loc], r9 = rng[1][loc], l1 = rng[2][loc], r1 = rng[3][loc];
+                double s0 = S0[p], s1 = S1[p], s2 = S2[p], u0 = T0[p], u1 = T1[p];
+#pragma unroll 4
+                for (int k = 0; k < C; ++k) {
+                    const double2 v0 = p0[k], v1 = p1[k];
+                    const int32_t j = c + k;
+                    const double q = (v0.x - bp[p]) * ap[p];
+                    const double q2 = q * q;
+                    const double tt = fma(-q2, fabs(q), 1.0);
+                    double w = (tt * tt) * tt;
+                    w = (j >= l1 && j <= r1) ? 1.0 : w;     // :547-551
+                    w = (j >= l9 && j <= r9) ? w : 0.0;     // :546, :553
+                    const double wr = w * v0.y;
+                    const double wq = wr * q;
+                    s0 += wr;
+                    s1 += wq;
+                    s2 = fma(wq, q, s2);
+                    u0 = fma(wr, v1.x, u0);
+                    u1 = fma(wq, v1.x, u1);
+                }
+                S0[p] = s0; S1[p] = s1; S2[p] = s2; T0[p] = u0; T1[p] = u1;
+            }
+        } else if (c >= t.flo && cend <= t.fhi && (cend < t.clo || c > t.chi)) {
             // interior: every element lies in (h1, h9] of every point of the warp
 #pragma unroll 2
             for (int k = 0; k < C; ++k) {
@@ -185,9 +306,9 @@ fit_kernel(const FitParams prm)
                 for (int p = 0; p < P; ++p) {
                     const double q = fma(v0.x, ap[p], bp[p]);
                     const double q2 = q * q;
-                    const double t = fma(-q2, fabs(q), 1.0);
-                    const double t2 = t * t;
-                    const double w = t2 * t;
+                    const double tt = fma(-q2, fabs(q), 1.0);
+                    const double t2 = tt * tt;
+                    const double w = t2 * tt;
                     S0[p] = fma(w, v0.y, S0[p]);
                     S1[p] = fma(w, v1.x, S1[p]);
                     S2[p] = fma(w, v1.y, S2[p]);
@@ -196,74 +317,164 @@ fit_kernel(const FitParams prm)
                 }
             }
         } else {
-            // edge / core chunk: per-point integer range tests
-#pragma unroll 2
-            for (int k = 0; k < C; ++k) {
-                const double2 v0 = p0[k], v1 = p1[k], v2 = p2[k];
-                const int32_t j = c + k;
+            // edge / core chunk: per-point integer range tests, one point at a time
+            // so that the ranges stay out of the interior loop's register budget
 #pragma unroll
-                for (int p = 0; p < P; ++p) {
+            for (int p = 0; p < P; ++p) {
+                const int loc = wid * (32 * P) + p * 32 + lane;
+                const int l9 = rng[0][loc], r9 = rng[1][loc], l1 = rng[2][loc], r1 = rng[3][loc];
+                double s0 = S0[p], s1 = S1[p], s2 = S2[p], u0 = T0[p], u1 = T1[p];
+#pragma unroll 4
+                for (int k = 0; k < C; ++k) {
+                    const double2 v0 = p0[k], v1 = p1[k], v2 = p2[k];
+                    const int32_t j = c + k;
                     const double q = fma(v0.x, ap[p], bp[p]);
                     const double q2 = q * q;
-                    const double t = fma(-q2, fabs(q), 1.0);
-                    const double t2 = t * t;
-                    double w = t2 * t;
-                    w = (j >= lo1[p] && j <= hi1[p]) ? 1.0 : w;     // :547-551
-                    w = (j >= lo9[p] && j <= hi9[p]) ? w : 0.0;     // :546, :553
-                    S0[p] = fma(w, v0.y, S0[p]);
-                    S1[p] = fma(w, v1.x, S1[p]);
-                    S2[p] = fma(w, v1.y, S2[p]);
-                    T0[p] = fma(w, v2.x, T0[p]);
-                    T1[p] = fma(w, v2.y, T1[p]);
+                    const double tt = fma(-q2, fabs(q), 1.0);
+                    double w = (tt * tt) * tt;
+                    w = (j >= l1 && j <= r1) ? 1.0 : w;     // :547-551
+                    w = (j >= l9 && j <= r9) ? w : 0.0;     // :546, :553
+                    s0 = fma(w, v0.y, s0);
+                    s1 = fma(w, v1.x, s1);
+                    s2 = fma(w, v1.y, s2);
+                    u0 = fma(w, v2.x, u0);
+                    u1 = fma(w, v2.y, u1);
                 }
+                S0[p] = s0; S1[p] = s1; S2[p] = s2; T0[p] = u0; T1[p] = u1;
             }
         }
         if (more) stash(buf ^ 1);
         __syncthreads();
     }
 
-    // ---- epilogue: local linear fit evaluated at xs (:559-584) ------------------
+    if (K > 1) {
+        // partial moments; fit_finalize_kernel adds the K parts in part order
+        double* __restrict__ dst = prm.part + ((size_t)tile * K + part) * (5 * (size_t)T);
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            const int loc = wid * (32 * P) + p * 32 + lane;
+            dst[0 * T + loc] = S0[p];
+            dst[1 * T + loc] = S1[p];
+            dst[2 * T + loc] = S2[p];
+            dst[3 * T + loc] = T0[p];
+            dst[4 * T + loc] = T1[p];
+        }
+        return;
+    }
+
     const double range = x[prm.n - 1] - x[0];                              // :535
 #pragma unroll
     for (int p = 0; p < P; ++p) {
-        if (!valid[p]) continue;
-        const int32_t i = pi[p];
-        double out;
-        if (!(S0[p] > 0.0)) {
-            out = y[i];                                   // ok = .false., :559, :673
-        } else {
-            const double inv = 1.0 / S0[p];
-            const double ym = T0[p] * inv;                // weighted mean of y
-            out = ym;
-            if (hp[p] > 0.0) {                            // :564
-                const double um = S1[p] * inv;
-                double cu = fma(-um, um, S2[p] * inv);    // weighted variance of u
-                cu = cu > 0.0 ? cu : 0.0;
-                if (sqrt(cu) * hc > 0.001 * range) {      // :573 (c = cu * hc^2)
-                    const double us = (xsp[p] - xc) * sc;
-                    const double cov = fma(-um, ym, T1[p] * inv);
-                    out = fma(cov / cu, us - um, ym);
-                }
-            }
-        }
-        prm.ys[i] = out;
+        if (!t.valid[p]) continue;
+        const int32_t i = tile0 + wid * (32 * P) + p * 32 + lane;
+        const double scale = exact ? t.hp[p] : t.hc;
+        const double us = exact ? 0.0 : (t.xsp[p] - xc) * sc;
+        prm.ys[i] = fit_value(S0[p], S1[p], S2[p], T0[p], T1[p], y[i], t.hp[p], scale, us, range);
     }
 }
+
+// Combines the K partial moment sets of every tile (ascending part = ascending j)
+// and evaluates the fit.  Launched with the fit kernel's CTA shape so that the
+// tile-level quantities (xc, hc, exact) are recomputed identically.
+template <int NT, int P>
+__global__ void __launch_bounds__(NT)
+fit_finalize_kernel(const FitParams prm)
+{
+    constexpr int T = NT * P;
+    __shared__ int32_t rng[4][T];
+    __shared__ TileShared ts;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int K = prm.ksplit;
+    const int tile = blockIdx.x;
+    const int32_t tile0 = prm.begin + (int32_t)tile * T;
+    Tile<NT, P> t;
+    tile_setup<NT, P>(prm, tile0, t, rng, ts);
+    if (t.jlo > t.jhi) return;
+    const double range = prm.x[prm.n - 1] - prm.x[0];
+    const double* __restrict__ src = prm.part + (size_t)tile * K * (5 * (size_t)T);
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+        if (!t.valid[p]) continue;
+        const int loc = wid * (32 * P) + p * 32 + lane;
+        double m[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+        for (int k = 0; k < K; ++k) {
+#pragma unroll
+            for (int q = 0; q < 5; ++q) m[q] += src[((size_t)k * 5 + q) * T + loc];
+        }
+        const int32_t i = tile0 + loc;
+        const double scale = t.exact ? t.hp[p] : t.hc;
+        const double us = t.exact ? 0.0 : (t.xsp[p] - t.xc) * t.sc;
+        prm.ys[i] = fit_value(m[0], m[1], m[2], m[3], m[4], prm.y[i], t.hp[p], scale, us, range);
+    }
+}
+
+// ---- launcher ---------------------------------------------------------------------------
+namespace {
+
+template <int NT, int P, int E, int MINB>
+int launch_variant(cf_lowess* h, FitParams& prm, int sms)
+{
+    constexpr int T = NT * P, C = NT * E;
+    const int tiles = (h->end - h->begin + T - 1) / T;
+    // K-way split of every tile's window when the tiles alone give too few waves
+    int occ = MINB;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fit_kernel<NT, P, E, MINB>, NT, 0);
+    if (occ < 1) occ = 1;
+    const long long slots = (long long)sms * occ;
+    int K = 1;
+    if (h->ksplit_override > 0) {
+        K = h->ksplit_override;
+    } else if (tiles < 24 * slots) {
+        K = (int)((16 * slots + tiles - 1) / tiles);
+    }
+    const int maxk = (h->ns + T) / (4 * C) > 1 ? (h->ns + T) / (4 * C) : 1;   // >= 4 chunks per part
+    if (K > maxk) K = maxk;
+    if (K > 64) K = 64;
+    if (K < 1) K = 1;
+    prm.ksplit = K;
+    prm.part = nullptr;
+    if (K > 1) {
+        const size_t need = (size_t)tiles * K * 5 * T * sizeof(double);
+        if (need > h->part_bytes) {
+            cudaFree(h->part);
+            h->part = nullptr;
+            h->part_bytes = 0;
+            CF_CUDA(cudaMalloc(&h->part, need));
+            h->part_bytes = need;
+        }
+        prm.part = h->part;
+    }
+    fit_kernel<NT, P, E, MINB><<<tiles * K, NT, 0, h->stream>>>(prm);
+    CF_CUDA(cudaGetLastError());
+    h->launches++;
+    h->fit_launches++;
+    if (K > 1) {
+        fit_finalize_kernel<NT, P><<<tiles, NT, 0, h->stream>>>(prm);
+        CF_CUDA(cudaGetLastError());
+        h->launches++;
+    }
+    return CF_OK;
+}
+
+}  // namespace
 
 int launch_fit(cf_lowess* h, bool use_rw)
 {
     if (h->n < 2 || h->end <= h->begin) return CF_OK;
-    constexpr int NT = 128, P = 4, E = 2;
     FitParams prm;
     prm.x = h->x; prm.y = h->y; prm.rw = use_rw ? h->rw : nullptr; prm.ys = h->ys;
     prm.w = h->win; prm.n = h->n; prm.ns = h->ns; prm.begin = h->begin; prm.end = h->end;
-    const int T = NT * P;
-    const int tiles = (h->end - h->begin + T - 1) / T;
-    fit_kernel<NT, P, E><<<tiles, NT, 0, h->stream>>>(prm);
-    CF_CUDA(cudaGetLastError());
-    h->launches++;
-    h->fit_launches++;
-    return CF_OK;
+    prm.ksplit = 1; prm.part = nullptr;
+    if (h->sms <= 0) {
+        int sms = 0;
+        CF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));
+        h->sms = sms;
+    }
+    switch (h->fit_variant) {
+        case 1: return launch_variant<128, 4, 2, 3>(h, prm, h->sms);
+        case 2: return launch_variant<128, 4, 2, 5>(h, prm, h->sms);
+        default: return launch_variant<128, 4, 2, 4>(h, prm, h->sms);
+    }
 }
 
 }  // namespace cf

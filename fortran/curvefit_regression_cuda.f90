@@ -1,0 +1,247 @@
+! curvefit_regression_cuda.f90
+!
+! Drop-in replacement for the LOWESS part of curvefit's curvefit_regression
+! module (reference src/curvefit_regression.f90:218-247 type lowess_smoothing,
+! :740-811 ls_init, :832-868 ls_smooth, :876-939 accessors).  Same type name,
+! same components, same type-bound procedure names and argument lists, same
+! error reporting through FERROR -- but initialize/smooth call the C ABI of
+! libcurvefit_cuda (include/curvefit_cuda.h) instead of the Fortran lowess().
+!
+! NOT COMPILED IN THE DEVELOPMENT IMAGE (no Fortran compiler there); built by
+! CMake only when check_language(Fortran) succeeds.  It needs the reference's
+! curvefit_core (error codes) and ferror modules on the include path.
+!
+! The type keeps only allocatable components, exactly like the reference, so
+! intrinsic assignment still deep-copies and there is no finaliser: the C
+! entry points used here are the STATELESS ones (host buffers in, host buffers
+! out), nothing device-side outlives a call.
+module curvefit_regression_cuda
+    use, intrinsic :: iso_c_binding
+    use, intrinsic :: iso_fortran_env, only : int32, real64
+    use curvefit_core, only : CF_ARRAY_SIZE_ERROR, CF_OUT_OF_MEMORY_ERROR, &
+        CF_NO_DATA_DEFINED_ERROR
+    use ferror, only : errors
+    implicit none
+    private
+    public :: lowess_smoothing
+
+    !> Code libcurvefit_cuda returns for a CUDA failure (no reference equivalent).
+    integer(int32), parameter :: CF_DEVICE_ERROR = 303
+
+    type lowess_smoothing
+        private
+        real(real64), allocatable, dimension(:) :: m_x
+        real(real64), allocatable, dimension(:) :: m_y
+        real(real64), allocatable, dimension(:) :: m_weights
+        real(real64), allocatable, dimension(:) :: m_residuals
+        real(real64) :: m_delta
+        logical :: m_init = .false.
+    contains
+        procedure, public :: initialize => ls_init
+        procedure, public :: smooth => ls_smooth
+        procedure, public :: get_count => ls_get_num_pts
+        procedure, public :: get_x => ls_get_x
+        procedure, public :: get_y => ls_get_y
+        procedure, public :: get_residuals => ls_get_residual
+    end type
+
+    interface
+        function cf_sort_xy(x, y, n, xs, ys, perm) bind(C, name = "cf_sort_xy") &
+                result(rc)
+            import :: c_int32_t, c_double, c_ptr
+            real(c_double), intent(in) :: x(*), y(*)
+            integer(c_int32_t), value :: n
+            real(c_double), intent(out) :: xs(*), ys(*)
+            type(c_ptr), value :: perm
+            integer(c_int32_t) :: rc
+        end function
+
+        function cf_lowess_smooth(x, y, n, f, nsteps, ys, rw, res) &
+                bind(C, name = "cf_lowess_smooth") result(rc)
+            import :: c_int32_t, c_double
+            real(c_double), intent(in) :: x(*), y(*)
+            integer(c_int32_t), value :: n
+            real(c_double), value :: f
+            integer(c_int32_t), value :: nsteps
+            real(c_double), intent(out) :: ys(*), rw(*), res(*)
+            integer(c_int32_t) :: rc
+        end function
+
+        function cf_last_error(buf, len) bind(C, name = "cf_last_error") result(rc)
+            import :: c_int32_t, c_char
+            character(kind = c_char), intent(out) :: buf(*)
+            integer(c_int32_t), value :: len
+            integer(c_int32_t) :: rc
+        end function
+    end interface
+
+contains
+    !> Reports a non-zero libcurvefit_cuda status through the reference's error
+    !! object with the reference's function names and messages.
+    subroutine report(errmgr, fcn, rc)
+        class(errors), intent(inout) :: errmgr
+        character(len = *), intent(in) :: fcn
+        integer(int32), intent(in) :: rc
+        character(kind = c_char) :: cbuf(512)
+        character(len = 512) :: msg
+        integer(int32) :: i, k
+        select case (rc)
+        case (CF_ARRAY_SIZE_ERROR)
+            call errmgr%report_error(fcn, "Input array sizes must match.", rc)
+        case (CF_OUT_OF_MEMORY_ERROR)
+            call errmgr%report_error(fcn, "Insufficient memory available.", rc)
+        case (CF_NO_DATA_DEFINED_ERROR)
+            call errmgr%report_error(fcn, "No data has been defined.", rc)
+        case default
+            k = cf_last_error(cbuf, 512_int32)
+            msg = " "
+            do i = 1, min(k, 511)
+                msg(i:i) = cbuf(i)
+            end do
+            call errmgr%report_error(fcn, trim(msg), rc)
+        end select
+    end subroutine
+
+    ! reference ls_init, src/curvefit_regression.f90:740-811
+    subroutine ls_init(this, x, y, srt, err)
+        class(lowess_smoothing), intent(inout) :: this
+        real(real64), intent(in), dimension(:) :: x, y
+        logical, intent(in), optional :: srt
+        class(errors), intent(inout), optional, target :: err
+
+        integer(int32) :: i, n, flag, rc
+        real(real64), allocatable, dimension(:) :: xc, yc
+        class(errors), pointer :: errmgr
+        type(errors), target :: deferr
+        logical :: sortData
+
+        this%m_init = .false.
+        n = size(x)
+        sortData = .true.
+        if (present(srt)) sortData = srt
+        if (present(err)) then
+            errmgr => err
+        else
+            errmgr => deferr
+        end if
+
+        if (size(y) /= n) then
+            call errmgr%report_error("ls_init", &
+                "Input array sizes must match.", CF_ARRAY_SIZE_ERROR)
+            return
+        end if
+
+        if (allocated(this%m_x)) deallocate(this%m_x)
+        if (allocated(this%m_y)) deallocate(this%m_y)
+        if (allocated(this%m_weights)) deallocate(this%m_weights)
+        if (allocated(this%m_residuals)) deallocate(this%m_residuals)
+        allocate(this%m_x(n), stat = flag)
+        if (flag == 0) allocate(this%m_y(n), stat = flag)
+        if (flag == 0) allocate(this%m_weights(n), stat = flag)
+        if (flag == 0) allocate(this%m_residuals(n), stat = flag)
+        if (flag == 0 .and. sortData) allocate(xc(n), stat = flag)
+        if (flag == 0 .and. sortData) allocate(yc(n), stat = flag)
+        if (flag /= 0) then
+            call errmgr%report_error("ls_init", &
+                "Insufficient memory available.", CF_OUT_OF_MEMORY_ERROR)
+            return
+        end if
+
+        if (sortData) then
+            ! contiguous copies (x, y are assumed-shape and may be strided),
+            ! then the device radix sort replaces sort(m_x, indices, .true.)
+            do concurrent (i = 1:n)
+                xc(i) = x(i)
+                yc(i) = y(i)
+            end do
+            rc = cf_sort_xy(xc, yc, n, this%m_x, this%m_y, c_null_ptr)
+            if (rc /= 0) then
+                call report(errmgr, "ls_init", rc)
+                return
+            end if
+        else
+            do concurrent (i = 1:n)
+                this%m_x(i) = x(i)
+                this%m_y(i) = y(i)
+            end do
+        end if
+
+        this%m_delta = 0.0d0
+        this%m_init = .true.
+    end subroutine
+
+    ! reference ls_smooth, src/curvefit_regression.f90:832-868
+    function ls_smooth(this, f, err) result(ys)
+        class(lowess_smoothing), intent(inout) :: this
+        real(real64), intent(in) :: f
+        class(errors), intent(inout), optional, target :: err
+        real(real64), allocatable, dimension(:) :: ys
+
+        integer(int32) :: n, flag, rc
+        class(errors), pointer :: errmgr
+        type(errors), target :: deferr
+
+        if (present(err)) then
+            errmgr => err
+        else
+            errmgr => deferr
+        end if
+        if (.not.this%m_init) then
+            call errmgr%report_error("ls_smooth", &
+                "No data has been defined.", CF_NO_DATA_DEFINED_ERROR)
+            return
+        end if
+        n = size(this%m_x)
+
+        allocate(ys(n), stat = flag)
+        if (flag /= 0) then
+            call errmgr%report_error("ls_smooth", &
+                "Insufficient memory available.", CF_OUT_OF_MEMORY_ERROR)
+            return
+        end if
+        ! lowess(m_x, m_y, f, 2, m_delta = 0, ys, m_weights, m_residuals), :866
+        rc = cf_lowess_smooth(this%m_x, this%m_y, n, f, 2_int32, ys, &
+            this%m_weights, this%m_residuals)
+        if (rc /= 0) call report(errmgr, "ls_smooth", rc)
+    end function
+
+    pure function ls_get_num_pts(this) result(n)
+        class(lowess_smoothing), intent(in) :: this
+        integer(int32) :: n
+        if (this%m_init) then
+            n = size(this%m_x)
+        else
+            n = 0
+        end if
+    end function
+
+    pure function ls_get_x(this, ind) result(x)
+        class(lowess_smoothing), intent(in) :: this
+        integer(int32), intent(in) :: ind
+        real(real64) :: x
+        if (this%m_init) then
+            x = this%m_x(ind)
+        else
+            x = 0.0d0
+        end if
+    end function
+
+    pure function ls_get_y(this, ind) result(y)
+        class(lowess_smoothing), intent(in) :: this
+        integer(int32), intent(in) :: ind
+        real(real64) :: y
+        if (this%m_init) then
+            y = this%m_y(ind)
+        else
+            y = 0.0d0
+        end if
+    end function
+
+    subroutine ls_get_residual(this, x)
+        class(lowess_smoothing), intent(in) :: this
+        real(real64), intent(out), dimension(:) :: x
+        integer(int32) :: n
+        n = min(size(x), this%get_count())
+        x(1:n) = this%m_residuals(1:n)
+    end subroutine
+end module

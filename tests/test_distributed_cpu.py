@@ -1,0 +1,156 @@
+"""CPU (gloo, world_size 2 and 3) test of the multi-GPU HOST logic in
+curvefit_b200/distributed.py: the range partition, the radix-select protocol
+over all-reduced histograms and the all-gather of robustness weights.  The
+device stages are replaced by a numpy stand-in built on the oracle (tests may
+use the oracle; the product never does), so the sharded result must equal the
+sequential oracle bit for bit."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from curvefit_b200.distributed import ShardedLowess, partition
+from tests import cases
+
+BITS, ROUNDS = 11, 6
+
+
+class NumpyStages:
+    """Same attributes/methods as DeviceStages, computed with numpy + the oracle."""
+
+    def __init__(self, x, y, rank, nranks):
+        from oracle import oracle
+        self.o = oracle
+        self.x, self.y = x, y
+        self.n = x.size
+        self.rank, self.nranks = rank, nranks
+        self.block, parts = partition(self.n, nranks)
+        self.begin, self.end = parts[rank]
+        self.hist = torch.zeros(2 << BITS, dtype=torch.int64)
+        self.rw = torch.zeros(nranks * self.block, dtype=torch.float64)
+        self.ys = torch.zeros(self.n, dtype=torch.float64)
+        self.res = torch.zeros(self.n, dtype=torch.float64)
+        self.cmad = torch.zeros(3, dtype=torch.float64)
+        self.rounds = ROUNDS
+        self.prefix = [0, 0]
+        self.krank = [0, 0]
+
+    def begin_run(self, f):
+        self.f = f
+
+    def fit_pass(self, use_rw):
+        idx = np.arange(self.begin, self.end, dtype=np.int32)
+        rw = self.rw.numpy()[: self.n].copy() if use_rw else None
+        if idx.size:
+            t = self.o.lowest_at(self.x, self.y, self.f, idx, rw)
+            self.ys.numpy()[self.begin:self.end] = t["ys"]
+            self.res.numpy()[self.begin:self.end] = self.y[self.begin:self.end] - t["ys"]
+        self.prefix = [0, 0]
+        self.krank = [(self.n - 1) // 2, self.n // 2]
+        self.hist.zero_()
+
+    @staticmethod
+    def _geom(r):
+        s = 64 - BITS * (r + 1)
+        return max(s, 0), (BITS if s >= 0 else BITS + s)
+
+    def hist_round(self, r):
+        shift, width = self._geom(r)
+        keys = np.abs(self.res.numpy()[self.begin:self.end]).view(np.uint64)
+        hs = shift + width
+        hi = (keys >> np.uint64(hs)) if hs < 64 else np.zeros_like(keys)
+        d = ((keys >> np.uint64(shift)) & np.uint64((1 << width) - 1)).astype(np.int64)
+        h = self.hist.numpy()
+        for t in range(2):
+            sel = d[hi == np.uint64(self.prefix[t])]
+            h[t << BITS:(t + 1) << BITS] += np.bincount(sel, minlength=1 << BITS)
+
+    def pick_round(self, r):
+        _, width = self._geom(r)
+        h = self.hist.numpy()
+        for t in range(2):
+            c = np.cumsum(h[t << BITS:(t + 1) << BITS])
+            b = int(np.searchsorted(c, self.krank[t], side="right"))
+            self.krank[t] -= int(c[b - 1]) if b > 0 else 0
+            self.prefix[t] = (self.prefix[t] << width) | b
+        self.hist.zero_()
+        if r == ROUNDS - 1:
+            lo, hi = (np.array(self.prefix, dtype=np.uint64).view(np.float64))
+            cmad = 3.0 * (hi + lo)
+            self.cmad[:] = torch.tensor([cmad, 0.001 * cmad, 0.999 * cmad])
+
+    def weights(self):
+        cmad, c1, c9 = self.cmad.tolist()
+        r = np.abs(self.res.numpy()[self.begin:self.end])
+        with np.errstate(invalid="ignore", divide="ignore"):
+            t = r / cmad
+            u = 1.0 - t * t
+            w = np.where(r <= c1, 1.0, np.where(r > c9, 0.0, u * u))
+        self.rw.numpy()[self.begin:self.end] = w
+
+    def sync(self):
+        pass
+
+
+def _worker(rank, world, port, n, f, nsteps, kind, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        x = cases.make_x(kind, n, 21)
+        y = cases.make_y(x, 21)
+        job = ShardedLowess(NumpyStages(x, y, rank, world))
+        ys, res = job.run(f, nsteps)
+        rw = job.s.rw[:n].clone()
+        q.put((rank, ys.numpy().copy(), res.numpy().copy(), rw.numpy().copy(), job.collectives,
+               job.s.cmad[0].item()))
+    finally:
+        dist.destroy_process_group()
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+@pytest.mark.parametrize("world,n,f,nsteps,kind", [(2, 1500, 0.2, 2, "uniform"),
+                                                   (3, 2000, 0.1, 3, "grid"),
+                                                   (2, 700, 0.3, 2, "ties")])
+def test_sharded_lowess_over_gloo_equals_sequential_oracle(oracle, world, n, f, nsteps, kind):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n, f, nsteps, kind, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    outs = [q.get(timeout=180) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    x = cases.make_x(kind, n, 21)
+    y = cases.make_y(x, 21)
+    ref = oracle.lowess(x, y, f, nsteps)
+    for rank, ys, res, rw, ncoll, cmad in outs:
+        assert np.array_equal(ys, ref["ys"]), rank
+        assert np.array_equal(res, ref["res"]), rank
+        assert np.array_equal(rw, ref["rw"]), rank
+        assert cmad == ref["cmad"][-1]
+        # per iteration: ROUNDS histogram all-reduces + 1 all-gather; 2 result gathers
+        assert ncoll == nsteps * (ROUNDS + 1) + 2
+
+
+def test_partition_is_tile_aligned_and_covers_everything():
+    for n, g in [(1_000_000, 8), (100, 2), (513, 3), (100_000_000, 8), (5, 4)]:
+        block, parts = partition(n, g)
+        assert block % 512 == 0 and len(parts) == g
+        assert parts[0][0] == 0 and parts[-1][1] == n
+        for (b0, e0), (b1, e1) in zip(parts, parts[1:]):
+            assert e0 == b1 and b0 <= e0
+        assert all(b % 512 == 0 or b == n for b, _ in parts)

@@ -61,7 +61,9 @@ def test_windows_bit_exact(cf, oracle, kind, n, f):
 
 
 @pytest.mark.parametrize("kind", ["grid", "uniform", "clustered", "ties", "equal", "wide"])
-@pytest.mark.parametrize("n,f,nsteps", [(2, 0.5, 2), (3, 1.0, 2), (100, 0.2, 2), (100, 0.8, 2),
+# (n = 3, f = 1 interpolates the end points exactly: its residuals are rounding noise, so
+# a robust iteration on them is chaotic in ANY implementation -- checked with nsteps = 0)
+@pytest.mark.parametrize("n,f,nsteps", [(2, 0.5, 2), (3, 1.0, 0), (100, 0.2, 2), (100, 0.8, 2),
                                         (1000, 0.05, 3), (4099, 0.3, 2), (513, 1.0, 1),
                                         (2048, 0.01, 2), (600, 0.4, 0), (3000, 0.2, 5)])
 def test_smooth_matches_oracle(cf, oracle, kind, n, f, nsteps):
@@ -73,8 +75,9 @@ def test_smooth_matches_oracle(cf, oracle, kind, n, f, nsteps):
     ys = fit.smooth(f, nsteps=nsteps)
     ok, d = cases.close(ys, ref["ys"], TOL)
     assert ok, ("ys", d)
-    ok, d = cases.close(fit.m_residuals, ref["res"], TOL)
-    assert ok, ("res", d)
+    # res = y - ys carries the ABSOLUTE error of ys, so its scale is y's, not its own
+    d = float(np.max(np.abs(fit.m_residuals - ref["res"])))
+    assert d <= TOL * max(float(np.max(np.abs(y))), 1e-300), ("res", d)
     if nsteps > 0:
         assert np.max(np.abs(fit.m_weights - ref["rw"])) <= 1e-9, "rw"
         assert abs(fit.last_stats.cmad_last - ref["cmad"][-1]) <= 1e-10 * max(ref["cmad"][-1], 1e-300)
@@ -132,14 +135,21 @@ def test_select_and_weights_bit_exact_given_same_residuals(cf, oracle):
 
 
 def test_zero_mad_and_dead_windows(cf, oracle):
+    """More than half of the residuals exactly zero -> cmad = 0 -> rw in {0, 1}
+    (:706-711); windows whose robustness weights are all zero -> ok = .false. ->
+    ys = y (:559, :673).  y is zero except a block of non-collinear outliers, so
+    the zero residuals are exact zeros in any arithmetic."""
     n = 60
     x = datagen.grid_x(n)
     y = np.zeros(n)
-    y[20:26] = 5.0
+    y[20:26] = [5.0, -3.0, 7.0, -4.0, 6.0, -2.0]
     ref = oracle.lowess(x, y, 0.1, 2)
+    assert ref["cmad"][-1] == 0.0 and set(np.unique(ref["rw"])) <= {0.0, 1.0}
     ys, rw, res = cf.cf_lowess_smooth(x, y, 0.1, 2)
     assert np.array_equal(rw, ref["rw"])
     assert cases.close(ys, ref["ys"], TOL)[0]
+    dead = np.nonzero(ref["ys"] == y)[0]
+    assert np.array_equal(ys[dead], y[dead])
 
 
 def test_sort_path_matches_ls_init(cf, oracle):
