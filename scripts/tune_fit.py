@@ -16,8 +16,8 @@ def main():
     y = datagen.noisy_y(x)
     ns = int(f * n)
     print("fp64 peak", regression.fp64_peak(-1, 200.0))
-    for variant in (0, 1, 2):
-        for ks in (0, 1, 2, 3, 4, 6, 8):
+    for variant in (0, 6, 7, 8, 9):
+        for ks in (0, 16):
             os.environ["CF_FIT_VARIANT"] = str(variant)
             os.environ["CF_FIT_KSPLIT"] = str(ks)
             fit = lowess_smoothing()
