@@ -42,6 +42,11 @@ WORKLOADS = {
     "c4": (100_000_000, 0.05, 3, "single series n=1e8 f=0.05 nsteps=3 (BASELINE headline; >15 min/step)"),
     "small": (100_000, 0.05, 3, "development size n=1e5 f=0.05 nsteps=3"),
 }
+# batched workloads: name -> (nseries, n, f, nsteps, description)
+BATCHED = {
+    "c3": (4096, 16384, 0.3, 2, "batched 4096 series x n=16384 f=0.3 nsteps=2 (BASELINE configs[2])"),
+    "c3small": (256, 16384, 0.3, 2, "development: 256 series x n=16384 f=0.3 nsteps=2"),
+}
 FLOP_PER_PAIR = 17.0
 BYTES_PER_POINT_PASS = 56.0
 
@@ -52,7 +57,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS) + sorted(BATCHED))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -313,12 +318,149 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+# ----------------------------------------------------------------------------
+# batched workloads (BASELINE configs[2]): independent series, partitioned over ranks
+# ----------------------------------------------------------------------------
+def make_batched(nseries, n, first=0):
+    from curvefit_b200 import datagen
+    x1 = datagen.grid_x(n)
+    base = datagen.signal(x1)
+    x = np.broadcast_to(x1, (nseries, n)).copy()
+    y = np.empty((nseries, n))
+    for k in range(nseries):
+        y[k] = base + (datagen.uniform01(datagen.SEED_Y + ((first + k) << 32), n) - 0.5)
+    return x, y
+
+
+def run_batched_reference(args):
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    nseries, n, f, nsteps, wname = BATCHED[args.workload]
+    from oracle import oracle
+    oracle.build()
+    cores = oracle.max_threads()
+    x, y = make_batched(2, n)
+    oracle.lowess_mt(x[0], y[0], f, nsteps)
+    vals = []
+    for _ in range(args.steps):
+        t0 = time.perf_counter()
+        for k in range(2):
+            oracle.lowess_mt(x[k], y[k], f, nsteps)
+        vals.append(2 * n / (time.perf_counter() - t0))
+    v = float(np.median(vals))
+    desc = f"2 of {nseries} series in full (oracle lowess on {cores} threads), scaled"
+    print(json.dumps({
+        "impl": "reference", "metric": "LOWESS fitted points/sec", "value": v, "unit": "points/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * nseries * n / v, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": wname, "nseries": nseries, "n": n, "f": f, "nsteps": nsteps},
+        "cpu_baseline": {"value": v, "unit": "points/s", "cores": cores, "kind": "port", "sample": desc},
+        "e2e": {"value": v, "unit": "points/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}), flush=True)
+
+
+def run_batched(args):
+    import torch
+    import torch.distributed as dist
+
+    from curvefit_b200 import _lib, regression
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    nseries, n, f, nsteps, wname = BATCHED[args.workload]
+    mine = nseries // world            # series are independent: partition, no collective
+    x, y = make_batched(mine, n, first=rank * mine)
+    ns = _lib.load().cf_lowess_span(n, f)
+    stream = torch.cuda.current_stream().cuda_stream
+    b = regression.batched_lowess(device=local, stream=stream)
+    b.initialize(x, y)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        b.run_resident(f, nsteps)
+    peak_tf, peak_mhz = regression.fp64_peak(local, 300.0) if rank == 0 else (0.0, 0.0)
+    barrier()
+    ms_steps, fit_ms, fit_launches, launches = [], 0.0, 0, 0
+    with Clocks(local) as clk:
+        for _ in range(args.steps):
+            flush.fill_(1)
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            st = b.run_resident(f, nsteps)
+            e1.record()
+            barrier()
+            ms = e0.elapsed_time(e1)
+            if world > 1:
+                t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                ms = float(t.item())
+            ms_steps.append(ms)
+            fit_ms += st.ms_fit
+            fit_launches += st.fit_launches
+            launches += st.launches
+    total_ms = float(sum(ms_steps))
+    if rank == 0:
+        value = mine * world * n * args.steps / (total_ms * 1e-3)
+        avg_ms = fit_ms / max(fit_launches, 1)
+        ach = FLOP_PER_PAIR * n * ns * mine / (avg_ms * 1e-3) / 1e12
+        line = {
+            "metric": "LOWESS fitted points/sec", "value": value, "unit": "points/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic",
+            "config": {"workload": wname, "nseries": nseries, "n": n, "f": f, "nsteps": nsteps, "ns": ns,
+                       "l2": "inputs larger than L2 (resident state > 2 GB per GPU) + 256 MiB flush",
+                       "parallelism": f"series partitioned x{world}, no collective"},
+            "gpu_launches": launches, "clocks": clk.summary(),
+            "roofline": {"bound": "fp64", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s",
+                         "frac": ach / peak_tf if peak_tf else None, "traffic": None,
+                         "kernel": "cf::fit_kernel", "avg_launch_ms": avg_ms,
+                         "share_of_step": fit_ms / total_ms,
+                         "peak_source": f"measured here: cf_fp64_peak ({peak_mhz:.0f} MHz equiv.)"},
+        }
+        if world == 1 and not args.no_e2e:
+            k = min(mine, 512)
+            xp = torch.from_numpy(x[:k].copy()).pin_memory().numpy()
+            yp = torch.from_numpy(y[:k].copy()).pin_memory().numpy()
+            regression.cf_lowess_smooth_batched(xp, yp, f, nsteps)
+            t0 = time.perf_counter()
+            regression.cf_lowess_smooth_batched(xp, yp, f, nsteps)
+            dt = time.perf_counter() - t0
+            line["e2e"] = {"value": k * n / dt, "unit": "points/s", "h2d_bytes_per_step": 16 * k * n,
+                           "d2h_bytes_per_step": 24 * k * n, "ms_per_step": dt * 1e3,
+                           "api": f"cf_lowess_smooth_batched on {k} of the series (host buffers, wall clock)"}
+        if world == 1 and not args.no_cpu_baseline:
+            from oracle import oracle
+            oracle.build()
+            t0 = time.perf_counter()
+            oracle.lowess_mt(x[0], y[0], f, nsteps)
+            dt = time.perf_counter() - t0
+            line["cpu_baseline"] = {"value": n / dt, "unit": "points/s", "cores": oracle.max_threads(),
+                                    "kind": "port", "sample": "1 series in full, oracle lowess on all threads"}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def main():
     args = parse()
+    batched = args.workload in BATCHED
     if args.impl == "reference":
-        run_reference(args)
+        run_batched_reference(args) if batched else run_reference(args)
     else:
-        run_ours(args)
+        run_batched(args) if batched else run_ours(args)
 
 
 if __name__ == "__main__":

@@ -8,6 +8,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
 #include <new>
 #include <vector>
 
@@ -55,9 +56,18 @@ static void free_buffers(cf_lowess* h)
     h->cap = h->cap_rw = 0;
 }
 
-static int reserve(cf_lowess* h, int32_t n)
+static int reserve(cf_lowess* h, int32_t n, int32_t nseries = 1)
 {
-    const int64_t need = n > 0 ? n : 1;
+    const int64_t need = (n > 0 ? (int64_t)n : 1) * (nseries > 0 ? nseries : 1);
+    if (nseries > h->sel_cap) {
+        cudaFree(h->hist); cudaFree(h->sel);
+        h->hist = nullptr; h->sel = nullptr; h->sel_cap = 0;
+        CF_CUDA(cudaMalloc(&h->hist, sizeof(unsigned long long) * kHistLen * (size_t)nseries));
+        CF_CUDA(cudaMalloc(&h->sel, sizeof(SelectState) * (size_t)nseries));
+        CF_CUDA(cudaMemsetAsync(h->hist, 0, sizeof(unsigned long long) * kHistLen * (size_t)nseries, h->stream));
+        CF_CUDA(cudaMemsetAsync(h->sel, 0, sizeof(SelectState) * (size_t)nseries, h->stream));
+        h->sel_cap = nseries;
+    }
     if (need > h->cap) {
         free_buffers(h);
         const size_t bd = sizeof(double) * (size_t)need, bi = sizeof(int32_t) * (size_t)need;
@@ -81,6 +91,7 @@ static int reserve_rw(cf_lowess* h)
 {
     int64_t need = (int64_t)h->nranks * h->block;
     if (need < h->n) need = h->n;
+    if (h->nseries > 1) need = (int64_t)h->n * h->nseries;   // batched: no sharding inside a series
     if (need < 1) need = 1;
     if (need > h->cap_rw) {
         cudaFree(h->rw);
@@ -187,11 +198,10 @@ int32_t cf_lowess_create(cf_lowess** out, int32_t device, void* stream)
         e = cudaEventCreate(&ev);
         if (e != cudaSuccess) { cf_lowess_destroy(h); return cuda_fail(e, "cudaEventCreate", __FILE__, __LINE__); }
     }
-    e = cudaMalloc(&h->hist, sizeof(unsigned long long) * kHistLen);
-    if (e == cudaSuccess) e = cudaMalloc(&h->sel, sizeof(SelectState));
-    if (e == cudaSuccess) e = cudaMemsetAsync(h->hist, 0, sizeof(unsigned long long) * kHistLen, h->stream);
-    if (e == cudaSuccess) e = cudaMemsetAsync(h->sel, 0, sizeof(SelectState), h->stream);
-    if (e != cudaSuccess) { cf_lowess_destroy(h); return cuda_fail(e, "cudaMalloc(select)", __FILE__, __LINE__); }
+    {
+        const int rc = reserve(h, 1, 1);   // select state + histograms for one series
+        if (rc != CF_OK) { cf_lowess_destroy(h); return rc; }
+    }
     *out = h;
     return CF_OK;
 }
@@ -218,6 +228,7 @@ static int32_t init_common(cf_lowess* h, const void* x, const void* y, int32_t n
     CF_TRY(use_device(h));
     h->init = false;                                   // :758
     h->win_f = -1.0;
+    h->nseries = 1;
     CF_TRY(reserve(h, n));
     h->n = n;
     compute_shard(h);
@@ -249,8 +260,36 @@ int32_t cf_lowess_init_device(cf_lowess* h, const void* d_x, const void* d_y, in
     return init_common(h, d_x, d_y, n, sort, cudaMemcpyDeviceToDevice);
 }
 
+int32_t cf_lowess_init_batched(cf_lowess* h, const double* x, const double* y, int32_t nseries,
+                               int32_t n)
+{
+    if (!h) { set_error("null handle"); return CF_INVALID_INPUT_ERROR; }
+    if (nseries < 1 || nseries > 32768 || n < 0 || (n > 0 && (!x || !y))) {
+        set_error("Input array sizes must match.");
+        return CF_ARRAY_SIZE_ERROR;
+    }
+    CF_TRY(use_device(h));
+    h->init = false;
+    h->win_f = -1.0;
+    h->rank = 0; h->nranks = 1;
+    CF_TRY(reserve(h, n, nseries));
+    h->n = n;
+    h->nseries = nseries;
+    compute_shard(h);
+    CF_TRY(reserve_rw(h));
+    const size_t bytes = sizeof(double) * (size_t)n * (size_t)nseries;
+    if (n > 0) {
+        CF_CUDA(cudaMemcpyAsync(h->x, x, bytes, cudaMemcpyHostToDevice, h->stream));
+        CF_CUDA(cudaMemcpyAsync(h->y, y, bytes, cudaMemcpyHostToDevice, h->stream));
+        CF_CUDA(cudaStreamSynchronize(h->stream));
+    }
+    h->init = true;
+    return CF_OK;
+}
+
 int32_t cf_lowess_set_shard(cf_lowess* h, int32_t rank, int32_t nranks)
 {
+    if (h && h->nseries > 1 && nranks > 1) { set_error("batched handles are not sharded"); return CF_INVALID_INPUT_ERROR; }
     if (!h || nranks < 1 || rank < 0 || rank >= nranks) { set_error("bad shard %d of %d", rank, nranks); return CF_INVALID_INPUT_ERROR; }
     CF_TRY(use_device(h));
     h->rank = rank;
@@ -332,7 +371,7 @@ int32_t cf_lowess_run(cf_lowess* h, double f, int32_t nsteps, cf_stats* st)
     CF_TRY(begin_stage(h, f));
     CF_CUDA(cudaEventRecord(h->ev[1], h->stream));
     if (h->n < 2) {                                                 // :651-654
-        if (h->n == 1) CF_CUDA(cudaMemcpyAsync(h->ys, h->y, sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+        if (h->n == 1) CF_CUDA(cudaMemcpyAsync(h->ys, h->y, sizeof(double) * (size_t)h->nseries, cudaMemcpyDeviceToDevice, h->stream));
         CF_CUDA(cudaStreamSynchronize(h->stream));
     } else {
         CF_TRY(run_passes(h, nsteps + 1, false, st));
@@ -371,7 +410,7 @@ int32_t cf_lowess_fetch(cf_lowess* h, double* ys, double* rw, double* res)
 {
     if (!h || !h->init) { set_error("No data has been defined."); return CF_NO_DATA_DEFINED_ERROR; }
     CF_TRY(use_device(h));
-    const size_t bytes = sizeof(double) * (size_t)h->n;
+    const size_t bytes = sizeof(double) * (size_t)h->n * (size_t)h->nseries;
     if (ys) CF_CUDA(cudaMemcpyAsync(ys, h->ys, bytes, cudaMemcpyDeviceToHost, h->stream));
     if (rw) CF_CUDA(cudaMemcpyAsync(rw, h->rw, bytes, cudaMemcpyDeviceToHost, h->stream));
     if (res) CF_CUDA(cudaMemcpyAsync(res, h->res, bytes, cudaMemcpyDeviceToHost, h->stream));
@@ -383,7 +422,7 @@ int32_t cf_lowess_fetch_xy(cf_lowess* h, double* xs, double* ysrt)
 {
     if (!h || !h->init) { set_error("No data has been defined."); return CF_NO_DATA_DEFINED_ERROR; }
     CF_TRY(use_device(h));
-    const size_t bytes = sizeof(double) * (size_t)h->n;
+    const size_t bytes = sizeof(double) * (size_t)h->n * (size_t)h->nseries;
     if (xs) CF_CUDA(cudaMemcpyAsync(xs, h->x, bytes, cudaMemcpyDeviceToHost, h->stream));
     if (ysrt) CF_CUDA(cudaMemcpyAsync(ysrt, h->y, bytes, cudaMemcpyDeviceToHost, h->stream));
     CF_CUDA(cudaStreamSynchronize(h->stream));
@@ -404,7 +443,7 @@ int32_t cf_lowess_windows(cf_lowess* h, double f, int32_t* nleft, int32_t* nrigh
     CF_TRY(use_device(h));
     CF_TRY(begin_stage(h, f));
     if (h->n < 2) return CF_OK;
-    const int32_t n = h->n;
+    const int32_t n = h->n * h->nseries;     // all series (indices stay per series)
     int32_t* tmp = nullptr;
     CF_CUDA(cudaMalloc(&tmp, sizeof(int32_t) * (size_t)n));
     struct { const int32_t* src; int32_t* dst; int32_t add; } jobs[] = {
@@ -494,6 +533,42 @@ int32_t cf_fp64_peak(int32_t device, double ms_target, double* tflops, double* s
 }
 
 // ---- stateless host-buffer entry points -------------------------------------------
+// The stateless calls keep one idle handle per device alive between calls so that a
+// caller looping over smooth() (the Fortran type does exactly that) pays for device
+// allocations, stream and event creation once, not per call.
+static std::mutex g_pool_mu;
+static std::vector<cf_lowess*> g_pool;
+
+static int32_t pool_acquire(cf_lowess** out)
+{
+    int dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess) {
+        std::lock_guard<std::mutex> lk(g_pool_mu);
+        for (size_t k = 0; k < g_pool.size(); ++k) {
+            if (g_pool[k]->device == dev) {
+                *out = g_pool[k];
+                g_pool.erase(g_pool.begin() + (long)k);
+                return CF_OK;
+            }
+        }
+    }
+    return cf_lowess_create(out, -1, nullptr);
+}
+
+static void pool_release(cf_lowess* h, int rc)
+{
+    if (!h) return;
+    if (rc == CF_OK) {
+        std::lock_guard<std::mutex> lk(g_pool_mu);
+        if (g_pool.size() < 8) {
+            h->rank = 0; h->nranks = 1;
+            g_pool.push_back(h);
+            return;
+        }
+    }
+    cf_lowess_destroy(h);
+}
+
 int32_t cf_sort_xy(const double* x, const double* y, int32_t n, double* x_sorted,
                    double* y_sorted, int32_t* perm)
 {
@@ -503,7 +578,7 @@ int32_t cf_sort_xy(const double* x, const double* y, int32_t n, double* x_sorted
     }
     if (n == 0) return CF_OK;
     cf_lowess* h = nullptr;
-    CF_TRY(cf_lowess_create(&h, -1, nullptr));
+    CF_TRY(pool_acquire(&h));
     int rc = CF_OK;
     double *dx = nullptr, *dy = nullptr, *ox = nullptr, *oy = nullptr;
     int32_t* dp = nullptr;
@@ -525,7 +600,7 @@ int32_t cf_sort_xy(const double* x, const double* y, int32_t n, double* x_sorted
         if (e != cudaSuccess) rc = cuda_fail(e, "cf_sort_xy download", __FILE__, __LINE__);
     }
     cudaFree(dx); cudaFree(dy); cudaFree(ox); cudaFree(oy); cudaFree(dp);
-    cf_lowess_destroy(h);
+    pool_release(h, rc);
     return rc;
 }
 
@@ -538,14 +613,14 @@ int32_t cf_lowess_smooth(const double* x_sorted, const double* y, int32_t n, dou
     }
     if (nsteps < 0) { set_error("nsteps must be >= 0"); return CF_INVALID_INPUT_ERROR; }
     cf_lowess* h = nullptr;
-    CF_TRY(cf_lowess_create(&h, -1, nullptr));
+    CF_TRY(pool_acquire(&h));
     int rc = cf_lowess_init(h, x_sorted, y, n, 0);
     if (rc == CF_OK) rc = cf_lowess_run(h, f, nsteps, nullptr);
     if (rc == CF_OK) {
         if (n < 2) rc = cf_lowess_fetch(h, ys, nullptr, nullptr);     // rw, res untouched (:651-654)
         else rc = cf_lowess_fetch(h, ys, nsteps > 0 ? rw : nullptr, res);
     }
-    cf_lowess_destroy(h);
+    pool_release(h, rc);
     return rc;
 }
 
@@ -557,18 +632,25 @@ int32_t cf_lowess_smooth_batched(const double* x_sorted, const double* y, int32_
     if (nsteps < 0) { set_error("nsteps must be >= 0"); return CF_INVALID_INPUT_ERROR; }
     if (nseries == 0 || n == 0) return CF_OK;
     if (!x_sorted || !y || !ys) { set_error("Input array sizes must match."); return CF_ARRAY_SIZE_ERROR; }
-    // independent series: a small pool of handles on their own streams keeps
-    // several series' kernels in flight so that short series still fill the GPU
-    const int pool = nseries < 8 ? nseries : 8;
-    std::vector<cf_lowess*> hs((size_t)pool, nullptr);
-    int rc = CF_OK;
-    for (int k = 0; k < pool && rc == CF_OK; ++k) rc = cf_lowess_create(&hs[(size_t)k], -1, nullptr);
-    auto enqueue = [&](cf_lowess* h, int32_t s) -> int {
-        const size_t off = (size_t)s * (size_t)n, bytes = sizeof(double) * (size_t)n;
+    // Independent series are a grid dimension of every kernel (blockIdx.y), so one
+    // launch covers a whole group of series; groups are bounded to ~2 GB of device
+    // state and alternate between two handles (streams) so that the copies of one
+    // group overlap the kernels of the other.
+    int64_t per = (int64_t)(2.0e9 / (64.0 * (double)n));
+    if (per < 1) per = 1;
+    if (per > 32768) per = 32768;            // gridDim.y limit is 65535
+    if (per > nseries) per = nseries;
+    cf_lowess* hs[2] = {nullptr, nullptr};
+    int rc = cf_lowess_create(&hs[0], -1, nullptr);
+    if (rc == CF_OK && per < nseries) rc = cf_lowess_create(&hs[1], -1, nullptr);
+    auto enqueue = [&](cf_lowess* h, int32_t s0, int32_t cnt) -> int {
+        const size_t off = (size_t)s0 * (size_t)n, bytes = sizeof(double) * (size_t)n * (size_t)cnt;
         h->init = false;
         h->win_f = -1.0;
-        CF_TRY(reserve(h, n));
+        h->rank = 0; h->nranks = 1;
+        CF_TRY(reserve(h, n, cnt));
         h->n = n;
+        h->nseries = cnt;
         compute_shard(h);
         CF_TRY(reserve_rw(h));
         CF_CUDA(cudaMemcpyAsync(h->x, x_sorted + off, bytes, cudaMemcpyHostToDevice, h->stream));
@@ -592,7 +674,15 @@ int32_t cf_lowess_smooth_batched(const double* x_sorted, const double* y, int32_
         }
         return CF_OK;
     };
-    for (int32_t s = 0; s < nseries && rc == CF_OK; ++s) rc = enqueue(hs[(size_t)(s % pool)], s);
+    int which = 0;
+    for (int64_t s0 = 0; s0 < nseries && rc == CF_OK; s0 += per, which ^= 1) {
+        cf_lowess* h = hs[which] ? hs[which] : hs[0];
+        // the handle's previous group must have left the device before its buffers are reused
+        cudaError_t e = cudaStreamSynchronize(h->stream);
+        if (e != cudaSuccess) { rc = cuda_fail(e, "batched smooth", __FILE__, __LINE__); break; }
+        const int32_t cnt = (int32_t)((nseries - s0) < per ? (nseries - s0) : per);
+        rc = enqueue(h, (int32_t)s0, cnt);
+    }
     for (cf_lowess* h : hs) {
         if (!h) continue;
         cudaError_t e = cudaStreamSynchronize(h->stream);

@@ -64,6 +64,7 @@ struct cf_lowess {
     cudaEvent_t ev[8] = {};
 
     int32_t n = 0;
+    int32_t nseries = 1;   // independent series of length n stored back to back (batched mode)
     bool init = false;
 
     // shard of the sorted index range fitted by this handle
@@ -76,8 +77,9 @@ struct cf_lowess {
     double win_f = -1.0;  // span fraction the stored windows were built for
     int32_t ns = 0;
 
-    unsigned long long* hist = nullptr;  // kHistLen counters
-    cf::SelectState* sel = nullptr;
+    unsigned long long* hist = nullptr;  // nseries x kHistLen counters
+    cf::SelectState* sel = nullptr;      // nseries states
+    int32_t sel_cap = 0;
 
     // fit kernel: partial-moment scratch for the K-way window split, tuning knobs
     double* part = nullptr;

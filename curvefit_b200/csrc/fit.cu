@@ -40,7 +40,21 @@ struct FitParams {
     double* part;       // [tile][K][5][T] partial moments when K > 1
     Windows w;
     int32_t n, ns, begin, end, ksplit;
+    int32_t tiles;      // tiles per series
 };
+
+// batched mode: series blockIdx.y occupies [series * n, (series + 1) * n) of every array
+__device__ __forceinline__ FitParams for_series(const FitParams& in, int series)
+{
+    FitParams p = in;
+    const size_t off = (size_t)series * (size_t)in.n;
+    p.x += off; p.y += off; p.ys += off;
+    if (p.rw) p.rw += off;
+    p.w.nleft += off; p.w.lo9 += off; p.w.hi9 += off;
+    p.w.lo1 += off; p.w.hi1 += off; p.w.leader += off;
+    if (p.part) p.part += (size_t)series * (size_t)in.tiles * in.ksplit * 5 * 512;
+    return p;
+}
 
 constexpr double kExactRatio = 16.0;
 
@@ -191,8 +205,9 @@ constexpr size_t fit_smem_bytes()
 
 template <int NT, int P, int E, int MINB, int U>
 __global__ void __launch_bounds__(NT, MINB)
-fit_kernel(const FitParams prm)
+fit_kernel(const FitParams prm_in)
 {
+    const FitParams prm = for_series(prm_in, blockIdx.y);
     constexpr int C = NT * E;      // window elements per staged chunk
     constexpr int T = NT * P;      // output points per tile
 
@@ -399,9 +414,11 @@ fit_kernel(const FitParams prm)
 // tile-level quantities (xc, hc, exact) are recomputed identically.
 template <int NT, int P>
 __global__ void __launch_bounds__(NT)
-fit_finalize_kernel(const FitParams prm)
+fit_finalize_kernel(const FitParams prm_in)
 {
+    const FitParams prm = for_series(prm_in, blockIdx.y);
     constexpr int T = NT * P;
+    static_assert(T == 512, "for_series() assumes 512-point tiles");
     __shared__ int32_t rng[4][T];
     __shared__ TileShared ts;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -444,6 +461,8 @@ int launch_variant(cf_lowess* h, FitParams& prm, int sms)
         attr_set = true;
     }
     const int tiles = (h->end - h->begin + T - 1) / T;
+    const long long all_tiles = (long long)tiles * h->nseries;
+    prm.tiles = tiles;
     // K-way split of every tile's window when the tiles alone give too few waves
     int occ = MINB;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, NT, smem);
@@ -452,8 +471,8 @@ int launch_variant(cf_lowess* h, FitParams& prm, int sms)
     int K = 1;
     if (h->ksplit_override > 0) {
         K = h->ksplit_override;
-    } else if (tiles < 48 * slots) {
-        K = (int)((32 * slots + tiles - 1) / tiles);
+    } else if (all_tiles < 48 * slots) {
+        K = (int)((32 * slots + all_tiles - 1) / all_tiles);
     }
     const int maxk = (h->ns + T) / (4 * C) > 1 ? (h->ns + T) / (4 * C) : 1;   // >= 4 chunks per part
     if (K > maxk) K = maxk;
@@ -462,7 +481,7 @@ int launch_variant(cf_lowess* h, FitParams& prm, int sms)
     prm.ksplit = K;
     prm.part = nullptr;
     if (K > 1) {
-        const size_t need = (size_t)tiles * K * 5 * T * sizeof(double);
+        const size_t need = (size_t)all_tiles * K * 5 * T * sizeof(double);
         if (need > h->part_bytes) {
             cudaFree(h->part);
             h->part = nullptr;
@@ -472,12 +491,12 @@ int launch_variant(cf_lowess* h, FitParams& prm, int sms)
         }
         prm.part = h->part;
     }
-    kern<<<tiles * K, NT, smem, h->stream>>>(prm);
+    kern<<<dim3(tiles * K, h->nseries), NT, smem, h->stream>>>(prm);
     CF_CUDA(cudaGetLastError());
     h->launches++;
     h->fit_launches++;
     if (K > 1) {
-        fit_finalize_kernel<NT, P><<<tiles, NT, 0, h->stream>>>(prm);
+        fit_finalize_kernel<NT, P><<<dim3(tiles, h->nseries), NT, 0, h->stream>>>(prm);
         CF_CUDA(cudaGetLastError());
         h->launches++;
     }

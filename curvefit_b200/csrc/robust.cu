@@ -15,10 +15,12 @@ namespace cf {
 __global__ void __launch_bounds__(256)
 residual_kernel(const double* __restrict__ y, double* __restrict__ ys,
                 double* __restrict__ res, const int32_t* __restrict__ leader,
-                int32_t begin, int32_t end)
+                int32_t begin, int32_t end, int32_t n)
 {
     const int32_t i = begin + blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= end) return;
+    const size_t off = (size_t)blockIdx.y * (size_t)n;     // batched: series offset
+    y += off; ys += off; res += off; leader += off;
     // a follower of a tie group takes the fitted value of the group's first
     // member (:685-688).  If that member belongs to the previous shard, the
     // shard's first point was fitted in its place (fit.cu, `valid`).
@@ -32,8 +34,8 @@ int launch_residuals(cf_lowess* h)
 {
     const int cnt = h->end - h->begin;
     if (cnt <= 0) return CF_OK;
-    residual_kernel<<<(cnt + 255) / 256, 256, 0, h->stream>>>(h->y, h->ys, h->res,
-                                                              h->win.leader, h->begin, h->end);
+    residual_kernel<<<dim3((cnt + 255) / 256, h->nseries), 256, 0, h->stream>>>(
+        h->y, h->ys, h->res, h->win.leader, h->begin, h->end, h->n);
     CF_CUDA(cudaGetLastError());
     h->launches++;
     return CF_OK;
@@ -53,6 +55,8 @@ __device__ __forceinline__ int sel_width(int round)
 
 __global__ void select_reset_kernel(SelectState* st, unsigned long long* hist, int32_t n)
 {
+    st += blockIdx.x;
+    hist += (size_t)blockIdx.x * kHistLen;
     for (int k = threadIdx.x; k < kHistLen; k += blockDim.x) hist[k] = 0ull;
     if (threadIdx.x == 0) {
         st->prefix[0] = st->prefix[1] = 0ull;
@@ -65,17 +69,20 @@ __global__ void select_reset_kernel(SelectState* st, unsigned long long* hist, i
 
 int launch_select_reset(cf_lowess* h)
 {
-    select_reset_kernel<<<1, 256, 0, h->stream>>>(h->sel, h->hist, h->n);
+    select_reset_kernel<<<h->nseries, 256, 0, h->stream>>>(h->sel, h->hist, h->n);
     CF_CUDA(cudaGetLastError());
     h->launches++;
     return CF_OK;
 }
 
 __global__ void __launch_bounds__(512)
-hist_kernel(const double* __restrict__ res, int32_t begin, int32_t end, int round,
+hist_kernel(const double* __restrict__ res, int32_t begin, int32_t end, int32_t n, int round,
             const SelectState* __restrict__ st, unsigned long long* __restrict__ hist)
 {
     __shared__ unsigned int sh[kHistLen];
+    res += (size_t)blockIdx.y * (size_t)n;
+    st += blockIdx.y;
+    hist += (size_t)blockIdx.y * kHistLen;
     for (int k = threadIdx.x; k < kHistLen; k += blockDim.x) sh[k] = 0u;
     __syncthreads();
     const int shift = sel_shift(round), width = sel_width(round);
@@ -102,7 +109,8 @@ int launch_hist(cf_lowess* h, int round)
     if (cnt <= 0) return CF_OK;
     int blocks = (cnt + 512 * 8 - 1) / (512 * 8);
     if (blocks > 148 * 4) blocks = 148 * 4;
-    hist_kernel<<<blocks, 512, 0, h->stream>>>(h->res, h->begin, h->end, round, h->sel, h->hist);
+    hist_kernel<<<dim3(blocks, h->nseries), 512, 0, h->stream>>>(h->res, h->begin, h->end, h->n,
+                                                                 round, h->sel, h->hist);
     CF_CUDA(cudaGetLastError());
     h->launches++;
     return CF_OK;
@@ -114,6 +122,8 @@ int launch_hist(cf_lowess* h, int round)
 __global__ void __launch_bounds__(64)
 pick_kernel(SelectState* st, unsigned long long* hist, int round)
 {
+    st += blockIdx.x;
+    hist += (size_t)blockIdx.x * kHistLen;
     const int t = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int width = sel_width(round);
     const int bins = 1 << width;
@@ -161,7 +171,7 @@ pick_kernel(SelectState* st, unsigned long long* hist, int round)
 
 int launch_pick(cf_lowess* h, int round)
 {
-    pick_kernel<<<1, 64, 0, h->stream>>>(h->sel, h->hist, round);
+    pick_kernel<<<h->nseries, 64, 0, h->stream>>>(h->sel, h->hist, round);
     CF_CUDA(cudaGetLastError());
     h->launches++;
     return CF_OK;
@@ -170,10 +180,12 @@ int launch_pick(cf_lowess* h, int round)
 // ---- bisquare robustness weights (:704-713) ---------------------------------------------
 __global__ void __launch_bounds__(256)
 bisquare_kernel(const double* __restrict__ res, double* __restrict__ rw,
-                const SelectState* __restrict__ st, int32_t begin, int32_t end)
+                const SelectState* __restrict__ st, int32_t begin, int32_t end, int32_t n)
 {
     const int32_t i = begin + blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= end) return;
+    const size_t off = (size_t)blockIdx.y * (size_t)n;
+    res += off; rw += off; st += blockIdx.y;
     const double cmad = st->cmad, c1 = st->c1, c9 = st->c9;
     const double r = fabs(res[i]);
     double w;
@@ -191,8 +203,8 @@ int launch_bisquare(cf_lowess* h)
 {
     const int cnt = h->end - h->begin;
     if (cnt <= 0) return CF_OK;
-    bisquare_kernel<<<(cnt + 255) / 256, 256, 0, h->stream>>>(h->res, h->rw, h->sel, h->begin,
-                                                              h->end);
+    bisquare_kernel<<<dim3((cnt + 255) / 256, h->nseries), 256, 0, h->stream>>>(
+        h->res, h->rw, h->sel, h->begin, h->end, h->n);
     CF_CUDA(cudaGetLastError());
     h->launches++;
     return CF_OK;

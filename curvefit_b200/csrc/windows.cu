@@ -17,6 +17,11 @@ windows_kernel(const double* __restrict__ x, int32_t n, int32_t ns, Windows w)
 {
     const int32_t i0 = blockIdx.x * blockDim.x + threadIdx.x;
     if (i0 >= n) return;
+    // batched mode: series blockIdx.y lives at offset blockIdx.y * n in every array;
+    // all indices stay relative to the series
+    const size_t off = (size_t)blockIdx.y * (size_t)n;
+    x += off;
+    w.nleft += off; w.lo9 += off; w.hi9 += off; w.lo1 += off; w.hi1 += off; w.leader += off;
 
     // tie group leader: first index whose x equals x[i0] (:683-689 -- with
     // delta = 0 the followers of a fitted point are the later identical x).
@@ -90,7 +95,7 @@ int launch_windows(cf_lowess* h, int32_t ns)
     if (h->n < 2) return CF_OK;
     const int threads = 256;
     const int blocks = (h->n + threads - 1) / threads;
-    windows_kernel<<<blocks, threads, 0, h->stream>>>(h->x, h->n, ns, h->win);
+    windows_kernel<<<dim3(blocks, h->nseries), threads, 0, h->stream>>>(h->x, h->n, ns, h->win);
     CF_CUDA(cudaGetLastError());
     h->launches++;
     return CF_OK;

@@ -187,6 +187,55 @@ class lowess_smoothing:
         x[:n] = self.m_residuals[:n]                          # :938
 
 
+class batched_lowess:
+    """nseries independent lowess_smoothing objects of equal length held on one GPU
+    and smoothed together (series are a grid dimension of every kernel).  Not part
+    of the reference's API: it is BASELINE config 3's device-resident form."""
+
+    def __init__(self, device: int = -1, stream: int = 0):
+        self._lib = _lib.load()
+        self._h = C.c_void_p()
+        rc = self._lib.cf_lowess_create(C.byref(self._h), device, C.c_void_p(stream) if stream else None)
+        if rc != 0:
+            self._h = C.c_void_p()
+            raise RuntimeError(f"cf_lowess_create failed ({rc}): {_lib.last_error()}")
+        self.shape = (0, 0)
+
+    def initialize(self, x, y) -> None:
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        y = np.ascontiguousarray(y, dtype=np.float64)
+        assert x.ndim == 2 and x.shape == y.shape
+        rc = self._lib.cf_lowess_init_batched(self._h, _dp(x), _dp(y), x.shape[0], x.shape[1])
+        if rc != 0:
+            raise RuntimeError(f"cf_lowess_init_batched failed ({rc}): {_lib.last_error()}")
+        self.shape = x.shape
+
+    def run_resident(self, f: float, nsteps: int = 2) -> "_lib.cf_stats":
+        st = _lib.cf_stats()
+        rc = self._lib.cf_lowess_run(self._h, float(f), int(nsteps), C.byref(st))
+        if rc != 0:
+            raise RuntimeError(f"cf_lowess_run failed ({rc}): {_lib.last_error()}")
+        return st
+
+    def fetch(self):
+        ys, rw, res = (np.empty(self.shape) for _ in range(3))
+        rc = self._lib.cf_lowess_fetch(self._h, _dp(ys), _dp(rw), _dp(res))
+        if rc != 0:
+            raise RuntimeError(f"cf_lowess_fetch failed ({rc}): {_lib.last_error()}")
+        return ys, rw, res
+
+    def close(self) -> None:
+        if self._h:
+            self._lib.cf_lowess_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 # ---- stateless wrappers over the host-buffer ABI (what the Fortran shim binds) --------
 def cf_sort_xy(x, y):
     lib = _lib.load()

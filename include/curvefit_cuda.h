@@ -115,6 +115,14 @@ CF_API int32_t cf_lowess_init(cf_lowess* h, const double* x, const double* y,
 CF_API int32_t cf_lowess_init_device(cf_lowess* h, const void* d_x, const void* d_y,
                                      int32_t n, int32_t sort);
 
+/* Batched variant: nseries independent series of equal length n, row-major
+ * [nseries][n], x already ascending per row (srt = .false. semantics).  Every
+ * later call on the handle (run, fetch, windows) then works on all series at
+ * once; each series is smoothed exactly as a separate lowess_smoothing object
+ * would be.  Sharding (cf_lowess_set_shard) does not apply to batched handles. */
+CF_API int32_t cf_lowess_init_batched(cf_lowess* h, const double* x, const double* y,
+                                      int32_t nseries, int32_t n);
+
 /* Restrict the fitted output points to block `rank` of `nranks` equal blocks
  * of the sorted index range (multi-GPU range partition).  Default 0 of 1. */
 CF_API int32_t cf_lowess_set_shard(cf_lowess* h, int32_t rank, int32_t nranks);

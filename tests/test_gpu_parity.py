@@ -199,6 +199,25 @@ def test_batched_matches_single(cf, oracle):
         assert cases.close(res[k], ref["res"], TOL)[0], k
 
 
+def test_batched_resident_handle_and_large_group(cf, oracle):
+    """Series as a grid dimension: 300 series of n = 700 (K-way split active), checked
+    in full for a few series; the resident handle gives the same bits as the
+    host-buffer entry point."""
+    s, n, f = 300, 700, 0.25
+    x = np.stack([np.sort(datagen.random_x(n, k)) for k in range(s)])
+    y = np.stack([datagen.noisy_y(x[k], k) for k in range(s)])
+    b = cf.batched_lowess()
+    b.initialize(x, y)
+    b.run_resident(f, 3)
+    ys, rw, res = b.fetch()
+    ys2, rw2, res2 = cf.cf_lowess_smooth_batched(x, y, f, 3)
+    assert np.array_equal(ys, ys2) and np.array_equal(rw, rw2) and np.array_equal(res, res2)
+    for k in (0, 1, 137, 299):
+        ref = oracle.lowess(x[k], y[k], f, 3)
+        assert cases.close(ys[k], ref["ys"], TOL)[0], k
+        assert np.max(np.abs(rw[k] - ref["rw"])) < 1e-9, k
+
+
 def test_shards_reproduce_the_single_gpu_result_bitwise(cf):
     """8e determinism: fitting block g of G gives bit-identical ys on that block."""
     import ctypes as C
