@@ -191,7 +191,7 @@ def run_ours(args):
     import torch.distributed as dist
 
     from curvefit_b200 import _lib, lowess_smoothing, regression
-    from curvefit_b200.distributed import DeviceStages, ShardedLowess
+    from curvefit_b200.distributed import DeviceStages, ShardedLowess, torch_stream_handle
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -204,7 +204,7 @@ def run_ours(args):
     lib = _lib.load()
     ns = lib.cf_lowess_span(n, f)
 
-    stream = torch.cuda.current_stream().cuda_stream
+    stream = torch_stream_handle()
     fit = lowess_smoothing(device=local, stream=stream)
     fit.initialize(x, y, srt=False)           # resident in HBM from here on
     stages = DeviceStages(fit, rank, world)
@@ -365,6 +365,7 @@ def run_batched(args):
     import torch.distributed as dist
 
     from curvefit_b200 import _lib, regression
+    from curvefit_b200.distributed import torch_stream_handle
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -376,7 +377,7 @@ def run_batched(args):
     mine = nseries // world            # series are independent: partition, no collective
     x, y = make_batched(mine, n, first=rank * mine)
     ns = _lib.load().cf_lowess_span(n, f)
-    stream = torch.cuda.current_stream().cuda_stream
+    stream = torch_stream_handle()
     b = regression.batched_lowess(device=local, stream=stream)
     b.initialize(x, y)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")

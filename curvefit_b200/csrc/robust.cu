@@ -63,7 +63,7 @@ __global__ void select_reset_kernel(SelectState* st, unsigned long long* hist, i
         // 1-based m2 = n - m1 + 1 <= m1 = 1 + n/2  ->  0-based (n-1)/2 and n/2   (:699-700)
         st->rank[0] = (unsigned long long)((n - 1) / 2);
         st->rank[1] = (unsigned long long)(n / 2);
-        st->cmad = st->c1 = st->c9 = 0.0;
+        // cmad, c1, c9 keep the previous iteration's values until pick_kernel's last round
     }
 }
 

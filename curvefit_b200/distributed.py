@@ -37,6 +37,15 @@ def partition(n: int, nranks: int, tile: int = 512):
     return per, out
 
 
+def torch_stream_handle() -> int:
+    """cudaStream_t of torch's current stream in the form libcurvefit_cuda expects.
+    torch's default stream is the legacy default stream, whose handle is 0 -- which
+    the C ABI reads as "create a private stream".  cudaStreamLegacy (0x1) names the
+    same stream explicitly, so kernels and NCCL collectives stay ordered."""
+    h = int(torch.cuda.current_stream().cuda_stream)
+    return h if h != 0 else 1
+
+
 class _DevArray:
     """Zero-copy view of a raw device pointer for torch.as_tensor."""
 
