@@ -48,6 +48,12 @@ BATCHED = {
     "c3small": (256, 16384, 0.3, 2, "development: 256 series x n=16384 f=0.3 nsteps=2"),
 }
 FLOP_PER_PAIR = 17.0
+# dram__bytes_read.sum + dram__bytes_write.sum of one fit_kernel launch, from the committed
+# `ncu --set full` captures (profiles/README.md); None where no capture exists.
+NCU_TRAFFIC = {
+    "c2": {"bytes": 53.1e6 + 349.3e6, "from": "profiles/r01_fit_kernel_c2_ncu_full.csv (K=10 window split "
+                                              "writes 400 MB of partial moments; 0.15% of DRAM peak)"},
+}
 BYTES_PER_POINT_PASS = 56.0
 
 
@@ -274,7 +280,9 @@ def run_ours(args):
             ach = flops / (avg_ms * 1e-3) / 1e12
             line["roofline"] = {
                 "bound": "fp64", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s",
-                "frac": ach / peak_tf if peak_tf else None, "traffic": None,
+                "frac": ach / peak_tf if peak_tf else None,
+                "traffic": NCU_TRAFFIC.get(args.workload, {}).get("bytes"),
+                "traffic_source": NCU_TRAFFIC.get(args.workload, {}).get("from"),
                 "kernel": "cf::fit_kernel", "avg_launch_ms": avg_ms,
                 "share_of_step": fit_ms / total_ms,
                 "peak_source": f"measured here: cf_fp64_peak DFMA microbenchmark ({peak_mhz:.0f} MHz equiv.; "
