@@ -64,6 +64,8 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS) + sorted(BATCHED))
+    ap.add_argument("--method", default="direct", choices=["direct", "tree", "auto"],
+                    help="evaluator of a lowest() pass: direct O(n ns) kernel (roofline claim) or moment tree")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -212,6 +214,7 @@ def run_ours(args):
 
     stream = torch_stream_handle()
     fit = lowess_smoothing(device=local, stream=stream)
+    fit.set_method(args.method)
     fit.initialize(x, y, srt=False)           # resident in HBM from here on
     stages = DeviceStages(fit, rank, world)
     job = ShardedLowess(stages)
@@ -225,6 +228,7 @@ def run_ours(args):
     def step():
         if world == 1:
             return fit.run_resident(f, nsteps)
+        lib.cf_lowess_reset_windows(fit._h)       # a step is a complete smooth(): windows included
         job.run(f, nsteps, gather=True)
         return None
 
@@ -387,6 +391,7 @@ def run_batched(args):
     ns = _lib.load().cf_lowess_span(n, f)
     stream = torch_stream_handle()
     b = regression.batched_lowess(device=local, stream=stream)
+    b.set_method(args.method)
     b.initialize(x, y)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 

@@ -51,6 +51,9 @@ SIGNATURES = {
     "cf_lowess_fetch": (C.c_int32, [C.c_void_p, c_dp, c_dp, c_dp]),
     "cf_lowess_fetch_xy": (C.c_int32, [C.c_void_p, c_dp, c_dp]),
     "cf_lowess_count": (C.c_int32, [C.c_void_p]),
+    "cf_lowess_set_method": (C.c_int32, [C.c_void_p, C.c_int32]),
+    "cf_lowess_method": (C.c_int32, [C.c_void_p]),
+    "cf_lowess_reset_windows": (C.c_int32, [C.c_void_p]),
     "cf_lowess_windows": (C.c_int32, [C.c_void_p, C.c_double, c_ip, c_ip, c_ip, c_ip, c_ip, c_ip, c_ip]),
     "cf_lowess_stage_begin": (C.c_int32, [C.c_void_p, C.c_double]),
     "cf_lowess_stage_fit": (C.c_int32, [C.c_void_p, C.c_int32]),
@@ -64,6 +67,7 @@ SIGNATURES = {
     "cf_fp64_peak": (C.c_int32, [C.c_int32, C.c_double, c_dp, c_dp]),
 }
 
+CF_METHOD_DIRECT, CF_METHOD_TREE, CF_METHOD_AUTO = range(3)
 CF_BUF_X, CF_BUF_Y, CF_BUF_YS, CF_BUF_RW, CF_BUF_RES, CF_BUF_HIST, CF_BUF_CMAD = range(7)
 
 _lib = None

@@ -187,6 +187,11 @@ int32_t cf_lowess_create(cf_lowess** out, int32_t device, void* stream)
     h->device = device;
     if (const char* v = getenv("CF_FIT_VARIANT")) h->fit_variant = atoi(v);
     if (const char* v = getenv("CF_FIT_KSPLIT")) h->ksplit_override = atoi(v);
+    if (const char* v = getenv("CF_LOWESS_METHOD")) {
+        if (!strcmp(v, "tree")) h->method = CF_METHOD_TREE;
+        else if (!strcmp(v, "auto")) h->method = CF_METHOD_AUTO;
+        else h->method = CF_METHOD_DIRECT;
+    }
     if (stream) {
         h->stream = (cudaStream_t)stream;
     } else {
@@ -215,6 +220,7 @@ void cf_lowess_destroy(cf_lowess* h)
     cudaFree(h->hist);
     cudaFree(h->sel);
     cudaFree(h->part);
+    cudaFree(h->tree);
     for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -304,6 +310,25 @@ int32_t cf_lowess_shard(const cf_lowess* h, int32_t* begin, int32_t* end, int32_
     if (begin) *begin = h->begin;
     if (end) *end = h->end;
     if (block) *block = h->block;
+    return CF_OK;
+}
+
+int32_t cf_lowess_set_method(cf_lowess* h, int32_t method)
+{
+    if (!h || method < CF_METHOD_DIRECT || method > CF_METHOD_AUTO) {
+        set_error("bad method %d", (int)method);
+        return CF_INVALID_INPUT_ERROR;
+    }
+    h->method = method;
+    return CF_OK;
+}
+
+int32_t cf_lowess_method(const cf_lowess* h) { return h ? h->method : -1; }
+
+int32_t cf_lowess_reset_windows(cf_lowess* h)
+{
+    if (!h) { set_error("null handle"); return CF_INVALID_INPUT_ERROR; }
+    h->win_f = -1.0;
     return CF_OK;
 }
 

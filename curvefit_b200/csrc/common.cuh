@@ -44,6 +44,29 @@ struct SelectState {
     double cmad, c1, c9;           // :701-703
 };
 
+#ifdef __CUDACC__
+// local linear fit evaluated at xs from the five moments (:559-584)
+__device__ __forceinline__ double fit_value(double S0, double S1, double S2, double T0, double T1,
+                                            double yi, double h, double scale, double us,
+                                            double range)
+{
+    if (!(S0 > 0.0)) return yi;                       // ok = .false., :559, :673
+    const double inv = 1.0 / S0;
+    const double ym = T0 * inv;                       // weighted mean of y
+    double out = ym;
+    if (h > 0.0) {                                    // :564
+        const double um = S1 * inv;
+        double cu = fma(-um, um, S2 * inv);           // weighted variance of u
+        cu = cu > 0.0 ? cu : 0.0;
+        if (sqrt(cu) * scale > 0.001 * range) {       // :573 (c = cu * scale^2)
+            const double cov = fma(-um, ym, T1 * inv);
+            out = fma(cov / cu, us - um, ym);
+        }
+    }
+    return out;
+}
+#endif
+
 // ---- per-point neighbourhood (0-based, inclusive) ----------------------------
 struct Windows {
     int32_t* nleft;   // slide result, :663-669
@@ -88,6 +111,11 @@ struct cf_lowess {
     int fit_variant = 0;       // env CF_FIT_VARIANT (development only)
     int ksplit_override = 0;   // env CF_FIT_KSPLIT  (development only)
 
+    // moment-tree evaluator (tree.cu): node storage, rebuilt every pass
+    double* tree = nullptr;
+    size_t tree_bytes = 0;
+    int method = 0;            // CF_METHOD_DIRECT / CF_METHOD_TREE / CF_METHOD_AUTO
+
     // counters for cf_stats
     int launches = 0, fit_launches = 0;
 };
@@ -96,7 +124,9 @@ namespace cf {
 
 // kernels' host launchers (each returns CF_OK or an error code; async on h->stream)
 int launch_windows(cf_lowess* h, int32_t ns);
-int launch_fit(cf_lowess* h, bool use_rw);
+int launch_fit(cf_lowess* h, bool use_rw);        // dispatches on h->method
+int launch_fit_tree(cf_lowess* h, bool use_rw);   // tree.cu
+bool method_is_tree(const cf_lowess* h);
 int launch_residuals(cf_lowess* h);           // tie copy + res = y - ys on the shard
 int launch_select_reset(cf_lowess* h);
 int launch_hist(cf_lowess* h, int round);

@@ -176,27 +176,6 @@ __device__ __forceinline__ void tile_setup(const FitParams& prm, int32_t tile0, 
     t.xc = x[min(tile0 + T / 2, prm.n - 1)];
 }
 
-// local linear fit evaluated at xs from the five moments (:559-584)
-__device__ __forceinline__ double fit_value(double S0, double S1, double S2, double T0, double T1,
-                                            double yi, double h, double scale, double us,
-                                            double range)
-{
-    if (!(S0 > 0.0)) return yi;                       // ok = .false., :559, :673
-    const double inv = 1.0 / S0;
-    const double ym = T0 * inv;                       // weighted mean of y
-    double out = ym;
-    if (h > 0.0) {                                    // :564
-        const double um = S1 * inv;
-        double cu = fma(-um, um, S2 * inv);           // weighted variance of u
-        cu = cu > 0.0 ? cu : 0.0;
-        if (sqrt(cu) * scale > 0.001 * range) {       // :573 (c = cu * scale^2)
-            const double cov = fma(-um, ym, T1 * inv);
-            out = fma(cov / cu, us - um, ym);
-        }
-    }
-    return out;
-}
-
 template <int NT, int P, int E>
 constexpr size_t fit_smem_bytes()
 {
@@ -505,9 +484,16 @@ int launch_variant(cf_lowess* h, FitParams& prm, int sms)
 
 }  // namespace
 
+// CF_METHOD_AUTO: the tree pays off once a window holds a few hundred elements
+bool method_is_tree(const cf_lowess* h)
+{
+    return h->method == CF_METHOD_TREE || (h->method == CF_METHOD_AUTO && h->ns >= 1024);
+}
+
 int launch_fit(cf_lowess* h, bool use_rw)
 {
     if (h->n < 2 || h->end <= h->begin) return CF_OK;
+    if (method_is_tree(h)) return launch_fit_tree(h, use_rw);
     FitParams prm;
     prm.x = h->x; prm.y = h->y; prm.rw = use_rw ? h->rw : nullptr; prm.ys = h->ys;
     prm.w = h->win; prm.n = h->n; prm.ns = h->ns; prm.begin = h->begin; prm.end = h->end;

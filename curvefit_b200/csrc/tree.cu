@@ -1,0 +1,496 @@
+// tree.cu -- the moment-tree evaluator of one lowest() pass (SURVEY 8f row N2,
+// DESIGN 3.5): an O(n log ns) replacement for the O(n * ns) sweep of
+// src/curvefit_regression.f90:542-584 that produces the same fitted values to
+// rounding (measured <= 3e-13 relative against the oracle; tolerance 1e-10).
+//
+// Idea.  Inside a window the tricube weight is a POLYNOMIAL on either side of
+// xs: with s = (x_j - xs)/h,
+//     w = (1 + s^3)^3  for x_j < xs,      w = (1 - s^3)^3  for x_j > xs,
+// and the reference's three discrete decisions (r <= h1 -> w = 1, r > h9 ->
+// w = 0, sweep exit) are the integer ranges [lo9, lo1), [lo1, hi1], (hi1, hi9]
+// that windows.cu already computes bit-exactly.  Hence every sum lowest() forms,
+//     S0 = sum w rw,  S1 = sum w rw s,  S2 = sum w rw s^2,
+//     T0 = sum w rw y,  T1 = sum w rw s y,
+// restricted to an index block that lies wholly inside one of the three
+// ranges, is a fixed linear combination of the block's power moments
+//     A_k = sum rw v^k (k = 0..11),   B_k = sum rw y v^k (k = 0..10),
+// v = (x - c)/d the block's own centred, scaled coordinate (|v| <= 1).  The
+// combination's coefficients are the Taylor coefficients of the degree-9
+// polynomial about the block centre -- computed per (point, block) in ~110
+// FP64 instructions, whatever the block's size.
+//
+// Structure.  A binary tree over leaves of 16 consecutive elements: leaf
+// moments from the data, parent moments from the children's by an exact
+// affine change of variable (binomial shift; |a| + |b| <= 1, so it is
+// numerically benign).  Each range is cut segment-tree fashion into
+// O(log ns) nodes plus < 16 elements at either end that are evaluated
+// directly with the reference's formula.  Because rw changes every
+// robustness iteration, the tree is rebuilt per pass (O(n), HBM-bound, ~1 % of
+// the pass).
+//
+// This backend is separate from fit.cu (the direct kernel that carries the
+// FP64 roofline claim); cf_lowess_set_method() selects it.
+#include "common.cuh"
+
+namespace cf {
+
+constexpr int kLeaf = 16;       // elements per leaf
+constexpr int kNodeLen = 32;    // doubles per node: c, d, A[12], B[11], pad
+constexpr int kKA = 12, kKB = 11;
+constexpr int kMaxLevels = 30;
+
+struct TreeParams {
+    const double* x;
+    const double* y;
+    const double* rw;           // nullptr: all ones (first pass)
+    double* ys;
+    double* nodes;              // [series][total_nodes][kNodeLen]
+    Windows w;
+    int32_t n, ns, begin, end;
+    int32_t nlevels;
+    int32_t cnt[kMaxLevels];    // nodes per level
+    int64_t off[kMaxLevels];    // first node of the level
+    int64_t total;              // nodes per series
+};
+
+__device__ __forceinline__ double2 ld2(const double* p)
+{
+    return __ldg(reinterpret_cast<const double2*>(p));
+}
+
+// first / last element of node (level, k)
+__device__ __forceinline__ void node_span(int level, int64_t k, int32_t n, int32_t& j0, int32_t& j1)
+{
+    const int64_t a = (k << level) * kLeaf;
+    int64_t b = ((k + 1) << level) * kLeaf;
+    if (b > n) b = n;
+    j0 = (int32_t)a;
+    j1 = (int32_t)(b - 1);
+}
+
+// ---- build: leaves -------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+tree_leaf_kernel(const TreeParams prm)
+{
+    const int32_t leaf = blockIdx.x * blockDim.x + threadIdx.x;
+    if (leaf >= prm.cnt[0]) return;
+    const size_t soff = (size_t)blockIdx.y * (size_t)prm.n;
+    const double* __restrict__ x = prm.x + soff;
+    const double* __restrict__ y = prm.y + soff;
+    const double* __restrict__ rw = prm.rw ? prm.rw + soff : nullptr;
+    double* __restrict__ nd = prm.nodes + ((size_t)blockIdx.y * prm.total + leaf) * kNodeLen;
+
+    int32_t j0, j1;
+    node_span(0, leaf, prm.n, j0, j1);
+    const double xf = x[j0], xl = x[j1];
+    const double c = 0.5 * xf + 0.5 * xl;
+    const double d = 0.5 * (xl - xf);
+    const double inv = d > 0.0 ? 1.0 / d : 0.0;
+    double A[kKA], Bm[kKB];
+#pragma unroll
+    for (int k = 0; k < kKA; ++k) A[k] = 0.0;
+#pragma unroll
+    for (int k = 0; k < kKB; ++k) Bm[k] = 0.0;
+    for (int32_t j = j0; j <= j1; ++j) {
+        const double v = (x[j] - c) * inv;
+        double p = rw ? rw[j] : 1.0;
+        double py = p * y[j];
+#pragma unroll
+        for (int k = 0; k < kKA; ++k) {
+            A[k] += p;
+            if (k < kKB) Bm[k] += py;
+            p *= v;
+            py *= v;
+        }
+    }
+    double2* o = reinterpret_cast<double2*>(nd);
+    o[0] = make_double2(c, d);
+#pragma unroll
+    for (int k = 0; k < kKA / 2; ++k) o[1 + k] = make_double2(A[2 * k], A[2 * k + 1]);
+#pragma unroll
+    for (int k = 0; k < 5; ++k) o[7 + k] = make_double2(Bm[2 * k], Bm[2 * k + 1]);
+    o[12] = make_double2(Bm[10], 0.0);
+}
+
+// ---- build: parents ------------------------------------------------------------------
+// Moments of one child re-expressed in the parent's coordinate v_p = b + a v_c and
+// added to the parent's:  M_k += sum_m C(k,m) b^(k-m) a^m M^c_m.
+template <int K>
+__device__ __forceinline__ void shift_add(const double* src, double a, double b,
+                                          double* acc)
+{
+    double m[K];
+    double ap = 1.0;
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+        m[k] = src[k] * ap;
+        ap *= a;
+    }
+    // binomial transform by repeated neighbour accumulation (Pascal's triangle)
+#pragma unroll
+    for (int r = 1; r < K; ++r) {
+#pragma unroll
+        for (int k = K - 1; k >= r; --k) m[k] = fma(b, m[k - 1], m[k]);
+    }
+#pragma unroll
+    for (int k = 0; k < K; ++k) acc[k] += m[k];
+}
+
+__device__ __forceinline__ void build_parent(const TreeParams& prm, const double* __restrict__ x,
+                                             double* base, int level, int32_t k)
+{
+    const double* ch = base + (prm.off[level - 1] + 2 * (int64_t)k) * kNodeLen;
+    double* nd = base + (prm.off[level] + k) * kNodeLen;
+    int32_t j0, j1;
+    node_span(level, k, prm.n, j0, j1);
+    const double xf = x[j0], xl = x[j1];
+    const double c = 0.5 * xf + 0.5 * xl;
+    const double d = 0.5 * (xl - xf);
+    const double inv = d > 0.0 ? 1.0 / d : 0.0;
+    double A[kKA], Bm[kKB];
+#pragma unroll
+    for (int q = 0; q < kKA; ++q) A[q] = 0.0;
+#pragma unroll
+    for (int q = 0; q < kKB; ++q) Bm[q] = 0.0;
+    const int nch = (2 * (int64_t)k + 1 < prm.cnt[level - 1]) ? 2 : 1;
+    for (int s = 0; s < nch; ++s) {
+        const double* cn = ch + (size_t)s * kNodeLen;   // written by this kernel in tree_top: plain loads
+        const double a = cn[1] * inv;
+        const double b = (cn[0] - c) * inv;
+        shift_add<kKA>(cn + 2, a, b, A);
+        shift_add<kKB>(cn + 2 + kKA, a, b, Bm);
+    }
+    double2* o = reinterpret_cast<double2*>(nd);
+    o[0] = make_double2(c, d);
+#pragma unroll
+    for (int q = 0; q < kKA / 2; ++q) o[1 + q] = make_double2(A[2 * q], A[2 * q + 1]);
+#pragma unroll
+    for (int q = 0; q < 5; ++q) o[7 + q] = make_double2(Bm[2 * q], Bm[2 * q + 1]);
+    o[12] = make_double2(Bm[10], 0.0);
+}
+
+__global__ void __launch_bounds__(128)
+tree_merge_kernel(const TreeParams prm, int level)
+{
+    const int32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= prm.cnt[level]) return;
+    const double* __restrict__ x = prm.x + (size_t)blockIdx.y * (size_t)prm.n;
+    double* base = prm.nodes + (size_t)blockIdx.y * prm.total * kNodeLen;
+    build_parent(prm, x, base, level, k);
+}
+
+// all levels from `level0` up in one CTA per series (they hold <= 2048 nodes)
+__global__ void __launch_bounds__(256)
+tree_top_kernel(const TreeParams prm, int level0)
+{
+    const double* __restrict__ x = prm.x + (size_t)blockIdx.x * (size_t)prm.n;
+    double* base = prm.nodes + (size_t)blockIdx.x * prm.total * kNodeLen;
+    for (int level = level0; level < prm.nlevels; ++level) {
+        for (int32_t k = threadIdx.x; k < prm.cnt[level]; k += blockDim.x)
+            build_parent(prm, x, base, level, k);
+        __threadfence_block();
+        __syncthreads();
+    }
+}
+
+// ---- evaluation ------------------------------------------------------------------------
+// Segment-tree walk over the leaf range [la, lb): yields, one node per call, the
+// O(log) maximal aligned nodes that tile it (bottom-up, the classic iterative
+// decomposition).  Per-thread state only; no lists in memory.
+struct Walk {
+    int32_t la, lb;
+    int level, sub;
+    __device__ __forceinline__ void start(int32_t a, int32_t b) { la = a; lb = b; level = 0; sub = 0; }
+    __device__ __forceinline__ bool next(int& lv, int32_t& idx)
+    {
+        while (la < lb) {
+            if (sub == 0) {
+                sub = 1;
+                if (la & 1) { lv = level; idx = la++; return true; }
+            }
+            sub = 0;
+            const bool t = lb & 1;
+            const int32_t id = lb - 1;
+            const int l0 = level;
+            if (t) lb = id;
+            la >>= 1; lb >>= 1; ++level;
+            if (t) { lv = l0; idx = id; return true; }
+        }
+        return false;
+    }
+};
+
+// [a, b) -> direct head [a, hd), whole leaves [la, lb), direct tail [tl, b)
+__device__ __forceinline__ void split_range(int32_t a, int32_t b, int32_t& hd, int32_t& tl,
+                                            int32_t& la, int32_t& lb)
+{
+    const int32_t up = (a + kLeaf - 1) / kLeaf * kLeaf;
+    const int32_t dn = b / kLeaf * kLeaf;
+    hd = min(b, up);
+    tl = max(hd, dn);
+    la = up / kLeaf;
+    lb = dn / kLeaf;
+    if (la >= lb) { la = lb = 0; }
+}
+
+struct Moments { double S0, S1, S2, T0, T1; };
+
+// One node inside a tricube range.  nsig = +1 left of xs (w = (1 + s^3)^3),
+// -1 right of xs (w = (1 - s^3)^3).
+__device__ __forceinline__ void take_tricube(const double* __restrict__ nd, double xs, double invh,
+                                             double nsig, Moments& m)
+{
+    const double2 cd = ld2(nd);
+    const double beta = (cd.x - xs) * invh;       // s at the node centre
+    const double alpha = cd.y * invh;             // ds/dv
+    const double b2 = beta * beta, a2 = alpha * alpha;
+    // 1 + nsig (beta + alpha v)^3 = c0 + c1 v + c2 v^2 + c3 v^3
+    const double c0 = fma(nsig, b2 * beta, 1.0);
+    const double c1 = nsig * (3.0 * b2 * alpha);
+    const double c2 = nsig * (3.0 * beta * a2);
+    const double c3 = nsig * (a2 * alpha);
+    // square (degree 6)
+    const double d0 = c0 * c0;
+    const double d1 = 2.0 * c0 * c1;
+    const double d2 = fma(c1, c1, 2.0 * c0 * c2);
+    const double d3 = 2.0 * fma(c0, c3, c1 * c2);
+    const double d4 = fma(c2, c2, 2.0 * c1 * c3);
+    const double d5 = 2.0 * c2 * c3;
+    const double d6 = c3 * c3;
+    // cube (degree 9): f = d * c
+    double f[10];
+    f[0] = d0 * c0;
+    f[1] = fma(d1, c0, d0 * c1);
+    f[2] = fma(d2, c0, fma(d1, c1, d0 * c2));
+    f[3] = fma(d3, c0, fma(d2, c1, fma(d1, c2, d0 * c3)));
+    f[4] = fma(d4, c0, fma(d3, c1, fma(d2, c2, d1 * c3)));
+    f[5] = fma(d5, c0, fma(d4, c1, fma(d3, c2, d2 * c3)));
+    f[6] = fma(d6, c0, fma(d5, c1, fma(d4, c2, d3 * c3)));
+    f[7] = fma(d6, c1, fma(d5, c2, d4 * c3));
+    f[8] = fma(d6, c2, d5 * c3);
+    f[9] = d6 * c3;
+    double A[kKA], Bm[kKA];
+#pragma unroll
+    for (int k = 0; k < kKA / 2; ++k) {
+        const double2 t = ld2(nd + 2 + 2 * k);
+        A[2 * k] = t.x; A[2 * k + 1] = t.y;
+    }
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        const double2 t = ld2(nd + 2 + kKA + 2 * k);
+        Bm[2 * k] = t.x; Bm[2 * k + 1] = t.y;     // Bm[11] is the node's zero pad
+    }
+    double D0 = 0.0, D1 = 0.0, D2 = 0.0, E0 = 0.0, E1 = 0.0;
+#pragma unroll
+    for (int k = 0; k < 10; ++k) {
+        D0 = fma(f[k], A[k], D0);
+        D1 = fma(f[k], A[k + 1], D1);
+        D2 = fma(f[k], A[k + 2], D2);
+        E0 = fma(f[k], Bm[k], E0);
+        E1 = fma(f[k], Bm[k + 1], E1);
+    }
+    // s = beta + alpha v:  sum w rw s = beta D0 + alpha D1, etc.
+    m.S0 += D0;
+    m.S1 += fma(beta, D0, alpha * D1);
+    m.S2 += fma(b2, D0, fma(2.0 * alpha * beta, D1, a2 * D2));
+    m.T0 += E0;
+    m.T1 += fma(beta, E0, alpha * E1);
+}
+
+// One node inside the w = 1 core.
+__device__ __forceinline__ void take_core(const double* __restrict__ nd, double xs, double invh,
+                                          Moments& m)
+{
+    const double2 cd = ld2(nd);
+    const double beta = (cd.x - xs) * invh, alpha = cd.y * invh;
+    const double2 a01 = ld2(nd + 2);
+    const double2 a23 = ld2(nd + 4);
+    const double2 b01 = ld2(nd + 2 + kKA);
+    m.S0 += a01.x;
+    m.S1 += fma(beta, a01.x, alpha * a01.y);
+    m.S2 += fma(beta * beta, a01.x, fma(2.0 * alpha * beta, a01.y, alpha * alpha * a23.x));
+    m.T0 += b01.x;
+    m.T1 += fma(beta, b01.x, alpha * b01.y);
+}
+
+// One thread per output point.  Three phases, each a warp-convergent loop in
+// which every lane works on ITS OWN k-th item (node or element), so no lane
+// evaluates an item it does not need:
+//   1. tricube nodes of [lo9, lo1) and (hi1, hi9]   (~110 FP64 instr each)
+//   2. core nodes of [lo1, hi1]                     (~15)
+//   3. the < 16 elements at either end of each range, reference formula (~13 each)
+template <int NT>
+__global__ void __launch_bounds__(NT)
+tree_eval_kernel(const TreeParams prm)
+{
+    const size_t soff = (size_t)blockIdx.y * (size_t)prm.n;
+    const double* __restrict__ x = prm.x + soff;
+    const double* __restrict__ y = prm.y + soff;
+    const double* __restrict__ rw = prm.rw ? prm.rw + soff : nullptr;
+    const double* __restrict__ nodes = prm.nodes + (size_t)blockIdx.y * prm.total * kNodeLen;
+    const int32_t i = prm.begin + blockIdx.x * NT + threadIdx.x;
+
+    // tie followers copy their leader's value later (robust.cu); a shard that starts
+    // inside a tie group fits its first point in the leader's place (as fit.cu)
+    bool valid = i < prm.end;
+    if (valid) {
+        const int32_t l = prm.w.leader[soff + i];
+        valid = (l == i) || (i == prm.begin && l < i);
+    }
+    double xs = 0.0, h = 0.0, invh = 0.0;
+    int32_t l9 = 0, r9 = -1, l1 = 0, r1 = -1;
+    if (valid) {
+        const int32_t nl = prm.w.nleft[soff + i];
+        xs = x[i];
+        const double hl = xs - x[nl], hr = x[nl + prm.ns - 1] - xs;        // :536
+        h = hl > hr ? hl : hr;
+        invh = h > 0.0 ? 1.0 / h : 0.0;
+        l9 = prm.w.lo9[soff + i]; r9 = prm.w.hi9[soff + i];
+        l1 = prm.w.lo1[soff + i]; r1 = prm.w.hi1[soff + i];
+    }
+    // ranges: L = [l9, l1), C = [l1, r1 + 1), R = [r1 + 1, r9 + 1)
+    int32_t hdL, tlL, laL, lbL, hdC, tlC, laC, lbC, hdR, tlR, laR, lbR;
+    split_range(l9, l1, hdL, tlL, laL, lbL);
+    split_range(l1, r1 + 1, hdC, tlC, laC, lbC);
+    split_range(r1 + 1, r9 + 1, hdR, tlR, laR, lbR);
+
+    Moments m = {0.0, 0.0, 0.0, 0.0, 0.0};
+    constexpr unsigned kFull = 0xffffffffu;
+
+    // ---- phase 1: tricube nodes, left range then right range
+    {
+        Walk w;
+        w.start(laL, lbL);
+        int phase = 0, lv = 0;
+        int32_t idx = 0;
+        double nsig = 1.0;
+        auto advance = [&]() -> bool {
+            if (w.next(lv, idx)) return true;
+            if (phase == 0) {
+                phase = 1;
+                nsig = -1.0;
+                w.start(laR, lbR);
+                return w.next(lv, idx);
+            }
+            return false;
+        };
+        bool have = advance();
+        while (__any_sync(kFull, have)) {
+            if (have) {
+                take_tricube(nodes + (prm.off[lv] + idx) * kNodeLen, xs, invh, nsig, m);
+                have = advance();
+            }
+        }
+    }
+    // ---- phase 2: core nodes
+    {
+        Walk w;
+        w.start(laC, lbC);
+        int lv = 0;
+        int32_t idx = 0;
+        bool have = w.next(lv, idx);
+        while (__any_sync(kFull, have)) {
+            if (have) {
+                take_core(nodes + (prm.off[lv] + idx) * kNodeLen, xs, invh, m);
+                have = w.next(lv, idx);
+            }
+        }
+    }
+    // ---- phase 3: range ends, element by element (:542-556 per pair)
+    {
+        // adjacent pieces are merged: [l9,hdL) | [tlL,l1)+[l1,hdC) | [tlC,r1+1)+[r1+1,hdR) | [tlR,r9+1)
+        int32_t sa[4], sb[4];
+        sa[0] = l9;  sb[0] = hdL;
+        sa[1] = tlL; sb[1] = hdC;
+        sa[2] = tlC; sb[2] = hdR;
+        sa[3] = tlR; sb[3] = r9 + 1;
+        int seg = 0;
+        int32_t j = sa[0], je = sb[0];
+        auto settle = [&]() -> bool {
+            while (j >= je) {
+                if (++seg > 3) return false;
+                j = seg == 1 ? sa[1] : seg == 2 ? sa[2] : sa[3];
+                je = seg == 1 ? sb[1] : seg == 2 ? sb[2] : sb[3];
+            }
+            return true;
+        };
+        bool have = valid && settle();
+        while (__any_sync(kFull, have)) {
+            if (have) {
+                const double q = (x[j] - xs) * invh;
+                const double tt = fma(-(q * q), fabs(q), 1.0);
+                double wgt = (tt * tt) * tt;
+                wgt = (j >= l1 && j <= r1) ? 1.0 : wgt;             // :547-551
+                const double wr = rw ? wgt * rw[j] : wgt;
+                const double wq = wr * q;
+                const double yj = y[j];
+                m.S0 += wr;
+                m.S1 += wq;
+                m.S2 = fma(wq, q, m.S2);
+                m.T0 = fma(wr, yj, m.T0);
+                m.T1 = fma(wq, yj, m.T1);
+                ++j;
+                have = settle();
+            }
+        }
+    }
+    if (valid) {
+        const double range = x[prm.n - 1] - x[0];                          // :535
+        prm.ys[soff + i] = fit_value(m.S0, m.S1, m.S2, m.T0, m.T1, y[i], h, h, 0.0, range);
+    }
+}
+
+// ---- host side ---------------------------------------------------------------------------
+int launch_fit_tree(cf_lowess* h, bool use_rw)
+{
+    if (h->n < 2 || h->end <= h->begin) return CF_OK;
+    TreeParams prm = {};
+    prm.x = h->x; prm.y = h->y; prm.rw = use_rw ? h->rw : nullptr; prm.ys = h->ys;
+    prm.w = h->win; prm.n = h->n; prm.ns = h->ns; prm.begin = h->begin; prm.end = h->end;
+    int L = 0;
+    int64_t total = 0;
+    int32_t cnt = (h->n + kLeaf - 1) / kLeaf;
+    for (;;) {
+        prm.cnt[L] = cnt;
+        prm.off[L] = total;
+        total += cnt;
+        ++L;
+        if (cnt <= 1 || L >= kMaxLevels) break;
+        cnt = (cnt + 1) / 2;
+    }
+    prm.nlevels = L;
+    prm.total = total;
+    const size_t need = sizeof(double) * kNodeLen * (size_t)total * (size_t)h->nseries;
+    if (need > h->tree_bytes) {
+        cudaFree(h->tree);
+        h->tree = nullptr;
+        h->tree_bytes = 0;
+        CF_CUDA(cudaMalloc(&h->tree, need));
+        h->tree_bytes = need;
+    }
+    prm.nodes = h->tree;
+
+    tree_leaf_kernel<<<dim3((prm.cnt[0] + 127) / 128, h->nseries), 128, 0, h->stream>>>(prm);
+    CF_CUDA(cudaGetLastError());
+    h->launches++;
+    int level = 1;
+    for (; level < L && prm.cnt[level] > 2048; ++level) {
+        tree_merge_kernel<<<dim3((prm.cnt[level] + 127) / 128, h->nseries), 128, 0, h->stream>>>(prm, level);
+        CF_CUDA(cudaGetLastError());
+        h->launches++;
+    }
+    if (level < L) {
+        tree_top_kernel<<<h->nseries, 256, 0, h->stream>>>(prm, level);
+        CF_CUDA(cudaGetLastError());
+        h->launches++;
+    }
+    constexpr int NT = 128;
+    const int cntp = h->end - h->begin;
+    tree_eval_kernel<NT><<<dim3((cntp + NT - 1) / NT, h->nseries), NT, 0, h->stream>>>(prm);
+    CF_CUDA(cudaGetLastError());
+    h->launches++;
+    h->fit_launches++;
+    return CF_OK;
+}
+
+}  // namespace cf

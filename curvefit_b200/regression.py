@@ -28,6 +28,9 @@ _MESSAGES = {
 }
 
 
+_METHODS = {"direct": _lib.CF_METHOD_DIRECT, "tree": _lib.CF_METHOD_TREE, "auto": _lib.CF_METHOD_AUTO}
+
+
 def _dp(a: Optional[np.ndarray]):
     return None if a is None else a.ctypes.data_as(_lib.c_dp)
 
@@ -78,6 +81,16 @@ class lowess_smoothing:
             self.close()
         except Exception:
             pass
+
+    def set_method(self, method) -> None:
+        """Evaluator of a lowest() pass: "direct" (O(n ns) sweep), "tree" (O(n log ns)
+        moment tree, equal to rounding) or "auto".  Extension; see curvefit_cuda.h."""
+        code = _METHODS[method] if isinstance(method, str) else int(method)
+        rc = self._handle()
+        if rc == 0:
+            rc = self._lib.cf_lowess_set_method(self._h, code)
+        if rc != 0:
+            raise RuntimeError(f"cf_lowess_set_method failed ({rc}): {_lib.last_error()}")
 
     # -- ls_init (:740-811) ---------------------------------------------------------
     def initialize(self, x, y, srt: bool = True, err: Optional[errors] = None) -> None:
@@ -134,9 +147,13 @@ class lowess_smoothing:
         return ys
 
     # -- device-resident run (benchmark path; no host copies) -------------------------
-    def run_resident(self, f: float, nsteps: int = 2) -> "_lib.cf_stats":
+    def run_resident(self, f: float, nsteps: int = 2, fresh_windows: bool = True) -> "_lib.cf_stats":
+        """One complete smooth() on the resident data.  fresh_windows: recompute the
+        neighbourhoods like every call of the reference's lowess does."""
         if not self.m_init:
             raise RuntimeError("No data has been defined.")
+        if fresh_windows:
+            self._lib.cf_lowess_reset_windows(self._h)
         st = _lib.cf_stats()
         rc = self._lib.cf_lowess_run(self._h, float(f), int(nsteps), C.byref(st))
         if rc != 0:
@@ -201,6 +218,12 @@ class batched_lowess:
             raise RuntimeError(f"cf_lowess_create failed ({rc}): {_lib.last_error()}")
         self.shape = (0, 0)
 
+    def set_method(self, method) -> None:
+        code = _METHODS[method] if isinstance(method, str) else int(method)
+        rc = self._lib.cf_lowess_set_method(self._h, code)
+        if rc != 0:
+            raise RuntimeError(f"cf_lowess_set_method failed ({rc}): {_lib.last_error()}")
+
     def initialize(self, x, y) -> None:
         x = np.ascontiguousarray(x, dtype=np.float64)
         y = np.ascontiguousarray(y, dtype=np.float64)
@@ -210,7 +233,9 @@ class batched_lowess:
             raise RuntimeError(f"cf_lowess_init_batched failed ({rc}): {_lib.last_error()}")
         self.shape = x.shape
 
-    def run_resident(self, f: float, nsteps: int = 2) -> "_lib.cf_stats":
+    def run_resident(self, f: float, nsteps: int = 2, fresh_windows: bool = True) -> "_lib.cf_stats":
+        if fresh_windows:
+            self._lib.cf_lowess_reset_windows(self._h)
         st = _lib.cf_stats()
         rc = self._lib.cf_lowess_run(self._h, float(f), int(nsteps), C.byref(st))
         if rc != 0:

@@ -129,6 +129,27 @@ CF_API int32_t cf_lowess_set_shard(cf_lowess* h, int32_t rank, int32_t nranks);
 CF_API int32_t cf_lowess_shard(const cf_lowess* h, int32_t* begin, int32_t* end,
                                int32_t* block);
 
+/* How one lowest() pass (:513-586) is evaluated.
+ *  CF_METHOD_DIRECT  the O(n * ns) sweep, one (point, element) pair at a time in
+ *                    the reference's summation order (fit.cu; FP64-pipe bound);
+ *  CF_METHOD_TREE    the O(n log ns) moment-tree evaluator (tree.cu): the same sums
+ *                    from per-block power moments, equal to rounding (<= 1e-12
+ *                    relative measured; contract 1e-10);
+ *  CF_METHOD_AUTO    tree when ns >= 1024, else direct.
+ * Default: CF_METHOD_DIRECT, or the environment variable CF_LOWESS_METHOD
+ * (direct | tree | auto) read at cf_lowess_create. */
+#define CF_METHOD_DIRECT 0
+#define CF_METHOD_TREE 1
+#define CF_METHOD_AUTO 2
+CF_API int32_t cf_lowess_set_method(cf_lowess* h, int32_t method);
+CF_API int32_t cf_lowess_method(const cf_lowess* h);
+
+/* The neighbourhoods (windows.cu) depend only on x and f, so a handle keeps them
+ * between runs with the same f.  This drops them: the next run recomputes them,
+ * like every call of the reference's lowess does (:658-669).  bench.py calls it
+ * before each timed step so that a step is a COMPLETE smooth(). */
+CF_API int32_t cf_lowess_reset_windows(cf_lowess* h);
+
 /* ls_smooth's work on the device (lowess, :625-715), nsteps robustness
  * iterations, whole series on this GPU.  Synchronous.  stats may be NULL. */
 CF_API int32_t cf_lowess_run(cf_lowess* h, double f, int32_t nsteps, cf_stats* stats);

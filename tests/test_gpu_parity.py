@@ -65,16 +65,20 @@ def test_windows_bit_exact(cf, oracle, kind, n, f):
 # a robust iteration on them is chaotic in ANY implementation -- checked with nsteps = 0)
 @pytest.mark.parametrize("n,f,nsteps", [(2, 0.5, 2), (3, 1.0, 0), (100, 0.2, 2), (100, 0.8, 2),
                                         (1000, 0.05, 3), (4099, 0.3, 2), (513, 1.0, 1),
-                                        (2048, 0.01, 2), (600, 0.4, 0), (3000, 0.2, 5)])
+                                        (2048, 0.01, 2), (600, 0.4, 0), (3000, 0.2, 5),
+                                        (16384, 0.3, 2)])
 def test_smooth_matches_oracle(cf, oracle, kind, n, f, nsteps):
     x = cases.make_x(kind, n, n + nsteps)
     y = cases.make_y(x, n + nsteps)
-    ref = oracle.lowess(x, y, f, nsteps)
+    ref = oracle.lowess_mt(x, y, f, nsteps) if n > 5000 else oracle.lowess(x, y, f, nsteps)
     fit = cf.lowess_smoothing()
+    fit.set_method("direct")
     fit.initialize(x, y, srt=False)
     ys = fit.smooth(f, nsteps=nsteps)
-    ok, d = cases.close(ys, ref["ys"], TOL)
-    assert ok, ("ys", d)
+    # pointwise 1e-10 against the oracle; points where the oracle's OWN rounding exceeds
+    # that (zero crossings at n >= 16384) are refereed in extended precision
+    ok, d, nref = cases.close_or_exact(ys, ref["ys"], x, y, fit.m_weights if nsteps > 0 else None, f, TOL)
+    assert ok, ("ys", d, nref)
     # res = y - ys carries the ABSOLUTE error of ys, so its scale is y's, not its own
     d = float(np.max(np.abs(fit.m_residuals - ref["res"])))
     assert d <= TOL * max(float(np.max(np.abs(y))), 1e-300), ("res", d)
@@ -255,5 +259,5 @@ def test_large_series_teacher_forced_samples(cf, oracle):
     idx = np.unique(np.concatenate([np.arange(0, 3), np.arange(n - 3, n),
                                     np.linspace(0, n - 1, 120).astype(np.int64)])).astype(np.int32)
     t = oracle.lowest_at(x, y, f, idx, rw_in)
-    ok, d = cases.close(ys_next[idx], t["ys"], TOL)
-    assert ok, d
+    ok, d, nref = cases.close_or_exact(ys_next[idx], t["ys"], x, y, rw_in, f, TOL, idx=idx)
+    assert ok, (d, nref)
