@@ -66,6 +66,10 @@ def parse():
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS) + sorted(BATCHED))
     ap.add_argument("--method", default="direct", choices=["direct", "tree", "auto"],
                     help="evaluator of a lowest() pass: direct O(n ns) kernel (roofline claim) or moment tree")
+    ap.add_argument("--transport", default="p2p", choices=["p2p", "nccl"],
+                    help="N > 1: exchange of the robustness step -- kernels over NVLink peer memory, or NCCL")
+    ap.add_argument("--no-tree", action="store_true",
+                    help="N = 1: skip the extra moment-tree measurements (same workload and n=1e8)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -217,6 +221,9 @@ def run_ours(args):
     fit.set_method(args.method)
     fit.initialize(x, y, srt=False)           # resident in HBM from here on
     stages = DeviceStages(fit, rank, world)
+    transport = "none"
+    if world > 1:
+        transport = "p2p" if (args.transport == "p2p" and stages.attach_peers()) else "nccl"
     job = ShardedLowess(stages)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
 
@@ -243,7 +250,7 @@ def run_ours(args):
             flush.fill_(1)
             barrier()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            l0 = stages.lib.cf_lowess_count(fit._h)  # cheap call; keeps ctypes warm
+            l0 = lib.cf_lowess_launch_count(fit._h)
             e0.record()
             st = step()
             e1.record()
@@ -257,12 +264,11 @@ def run_ours(args):
             if st is not None:
                 fit_ms += st.ms_fit
                 fit_launches += st.fit_launches
-                launches += st.launches
+            launches += lib.cf_lowess_launch_count(fit._h) - l0
     total_ms = float(sum(ms_steps))
     value = n * args.steps / (total_ms * 1e-3)
-    if world > 1:
-        # launches per step on this rank: fit+res+reset per pass, 2 per select round, bisquare
-        launches = args.steps * ((nsteps + 1) * 3 + nsteps * (2 * stages.rounds + 1) + 2)
+    if world > 1 and stages.p2p and stages.peer_error():
+        raise RuntimeError("a peer-memory wait timed out during the timed region")
 
     line = None
     if rank == 0:
@@ -274,7 +280,9 @@ def run_ours(args):
             "config": {"workload": wname, "n": n, "f": f, "nsteps": nsteps, "ns": ns,
                        "x": "grid (i-1)*dx", "y": "0.5sin20x+cos5x*exp(-.1x)+U(-.5,.5) splitmix64",
                        "l2": "256 MiB flush write between timed steps",
-                       "parallelism": f"range-sharded x{world}" if world > 1 else "single GPU"},
+                       "parallelism": f"range-sharded x{world}" if world > 1 else "single GPU",
+                       "method": args.method, "transport": transport},
+            "gpu_launches_note": "kernels of libcurvefit_cuda launched by rank 0 inside the timed region",
             "gpu_launches": launches,
             "clocks": clk.summary(),
         }
@@ -313,8 +321,34 @@ def run_ours(args):
         line["e2e"] = {"value": n / dt, "unit": "points/s", "h2d_bytes_per_step": 16 * n,
                        "d2h_bytes_per_step": 24 * n, "ms_per_step": dt * 1e3,
                        "api": "cf_lowess_smooth(host x, y -> host ys, rw, res), pinned buffers, wall clock"}
+    elif world > 1 and not args.no_e2e:
+        # every rank uploads the series from pinned host memory, the ranks smooth it together,
+        # rank 0 reads ys, rw, res back -- all inside the timed region, max over ranks
+        xp = torch.from_numpy(x).pin_memory().numpy()
+        yp = torch.from_numpy(y).pin_memory().numpy()
+        outs = tuple(torch.empty(n, dtype=torch.float64).pin_memory().numpy() for _ in range(3)) if rank == 0 else None
+        job.smooth_host(xp, yp, f, nsteps, outs)
+        reps = max(1, min(args.steps, 3))
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            job.smooth_host(xp, yp, f, nsteps, outs)
+        barrier()
+        t = torch.tensor([(time.perf_counter() - t0) / reps], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t.item())
+        if rank == 0:
+            line["e2e"] = {"value": n / dt, "unit": "points/s", "h2d_bytes_per_step": 16 * n * world,
+                           "d2h_bytes_per_step": 24 * n, "ms_per_step": dt * 1e3,
+                           "api": "ShardedLowess.smooth_host(host x, y on every rank -> host ys, rw, res on "
+                                  "rank 0), pinned buffers, wall clock, max over ranks"}
     elif rank == 0:
         line["e2e"] = None
+
+    # ---- moment-tree evaluator beside the direct kernel (N = 1 only) -----------------------
+    # Own accounting: never part of `value` or of the direct kernel's roofline.
+    if world == 1 and args.method == "direct" and not args.no_tree:
+        line["tree"] = tree_numbers(args, fit, flush, x, y, f, nsteps)
 
     # ---- CPU baseline on the host cores (rank 0, N = 1 only) ----------------------------
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -326,8 +360,54 @@ def run_ours(args):
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
+        stages.detach_peers()
         dist.barrier()
         dist.destroy_process_group()
+
+
+def tree_numbers(args, fit, flush, x, y, f, nsteps):
+    """The O(n log ns) moment-tree evaluator (csrc/tree.cu) on the bench workload and on the
+    BASELINE headline series (n = 1e8, f = 0.05, 3 robustness iterations), device-resident,
+    CUDA-event timed per step with the L2 flush in between; plus its largest deviation from
+    the direct kernel's ys on the bench workload."""
+    import torch
+
+    from curvefit_b200 import lowess_smoothing
+    from curvefit_b200.regression import _dp
+
+    def timed(obj, ff, k, reps):
+        obj.run_resident(ff, k)
+        ms = []
+        for _ in range(reps):
+            flush.fill_(1)
+            torch.cuda.synchronize()
+            ms.append(obj.run_resident(ff, k).ms_total)
+        return float(np.median(ms))
+
+    out = {}
+    ys_direct = np.empty(x.size)
+    fit._lib.cf_lowess_fetch(fit._h, _dp(ys_direct), None, None)
+    fit.set_method("tree")
+    ms = timed(fit, f, nsteps, max(args.steps, 3))
+    ys_tree = np.empty(x.size)
+    fit._lib.cf_lowess_fetch(fit._h, _dp(ys_tree), None, None)
+    fit.set_method("direct")
+    out["same_workload"] = {"value": x.size / (ms * 1e-3), "unit": "points/s", "ms_per_step": ms,
+                            "max_abs_diff_vs_direct": float(np.max(np.abs(ys_tree - ys_direct))),
+                            "max_abs_ys": float(np.max(np.abs(ys_direct)))}
+    n4, f4, k4, name4 = WORKLOADS["c4"]
+    if x.size != n4:
+        x4, y4 = make_data(n4)
+        big = lowess_smoothing(device=fit._device, stream=fit._stream)
+        big.set_method("tree")
+        big.initialize(x4, y4, srt=False)
+        ms4 = timed(big, f4, k4, 2)
+        out["headline_n1e8"] = {"workload": name4.split(" (")[0], "value": n4 / (ms4 * 1e-3), "unit": "points/s",
+                                "ms_per_step": ms4}
+        big.close()
+    out["note"] = ("moment-tree evaluator, equal to the direct kernel to rounding (tolerance 1e-10); "
+                   "separate accounting from `value` / `roofline`")
+    return out
 
 
 # ----------------------------------------------------------------------------

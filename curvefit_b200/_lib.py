@@ -51,6 +51,7 @@ SIGNATURES = {
     "cf_lowess_fetch": (C.c_int32, [C.c_void_p, c_dp, c_dp, c_dp]),
     "cf_lowess_fetch_xy": (C.c_int32, [C.c_void_p, c_dp, c_dp]),
     "cf_lowess_count": (C.c_int32, [C.c_void_p]),
+    "cf_lowess_launch_count": (C.c_int64, [C.c_void_p]),
     "cf_lowess_set_method": (C.c_int32, [C.c_void_p, C.c_int32]),
     "cf_lowess_method": (C.c_int32, [C.c_void_p]),
     "cf_lowess_reset_windows": (C.c_int32, [C.c_void_p]),
@@ -61,6 +62,13 @@ SIGNATURES = {
     "cf_lowess_stage_pick": (C.c_int32, [C.c_void_p, C.c_int32]),
     "cf_lowess_stage_weights": (C.c_int32, [C.c_void_p]),
     "cf_lowess_select_rounds": (C.c_int32, []),
+    "cf_lowess_peer_handle_bytes": (C.c_int32, []),
+    "cf_lowess_peer_export": (C.c_int32, [C.c_void_p, C.c_void_p]),
+    "cf_lowess_peer_attach": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32]),
+    "cf_lowess_peer_detach": (C.c_int32, [C.c_void_p]),
+    "cf_lowess_peer_attached": (C.c_int32, [C.c_void_p]),
+    "cf_lowess_peer_error": (C.c_int32, [C.c_void_p, c_ip]),
+    "cf_lowess_stage_gather": (C.c_int32, [C.c_void_p]),
     "cf_lowess_sync": (C.c_int32, [C.c_void_p]),
     "cf_lowess_buffer": (C.c_void_p, [C.c_void_p, C.c_int32]),
     "cf_lowess_hist_len": (C.c_int32, []),

@@ -46,8 +46,11 @@ static void compute_shard(cf_lowess* h)
     h->end = (int32_t)(b + per < n ? b + per : n);
 }
 
+// Exported (IPC-mapped) buffers are about to be freed: the mapping of the peers'
+// buffers is dropped here; the peers must export / attach again as well.
 static void free_buffers(cf_lowess* h)
 {
+    peer_detach(h);
     cudaFree(h->x); cudaFree(h->y); cudaFree(h->ys); cudaFree(h->rw); cudaFree(h->res);
     cudaFree(h->win.nleft); cudaFree(h->win.lo9); cudaFree(h->win.hi9);
     cudaFree(h->win.lo1); cudaFree(h->win.hi1); cudaFree(h->win.leader);
@@ -60,8 +63,9 @@ static int reserve(cf_lowess* h, int32_t n, int32_t nseries = 1)
 {
     const int64_t need = (n > 0 ? (int64_t)n : 1) * (nseries > 0 ? nseries : 1);
     if (nseries > h->sel_cap) {
-        cudaFree(h->hist); cudaFree(h->sel);
-        h->hist = nullptr; h->sel = nullptr; h->sel_cap = 0;
+        cudaFree(h->hist); cudaFree(h->sel); cudaFree(h->span);
+        h->hist = nullptr; h->sel = nullptr; h->span = nullptr; h->sel_cap = 0;
+        CF_CUDA(cudaMalloc(&h->span, sizeof(int32_t) * 2 * (size_t)nseries));
         CF_CUDA(cudaMalloc(&h->hist, sizeof(unsigned long long) * kHistLen * (size_t)nseries));
         CF_CUDA(cudaMalloc(&h->sel, sizeof(SelectState) * (size_t)nseries));
         CF_CUDA(cudaMemsetAsync(h->hist, 0, sizeof(unsigned long long) * kHistLen * (size_t)nseries, h->stream));
@@ -94,6 +98,7 @@ static int reserve_rw(cf_lowess* h)
     if (h->nseries > 1) need = (int64_t)h->n * h->nseries;   // batched: no sharding inside a series
     if (need < 1) need = 1;
     if (need > h->cap_rw) {
+        peer_detach(h);
         cudaFree(h->rw);
         h->rw = nullptr;
         h->cap_rw = 0;
@@ -217,8 +222,10 @@ void cf_lowess_destroy(cf_lowess* h)
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     free_buffers(h);
+    cudaFree(h->comm);
     cudaFree(h->hist);
     cudaFree(h->sel);
+    cudaFree(h->span);
     cudaFree(h->part);
     cudaFree(h->tree);
     for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
@@ -298,6 +305,10 @@ int32_t cf_lowess_set_shard(cf_lowess* h, int32_t rank, int32_t nranks)
     if (h && h->nseries > 1 && nranks > 1) { set_error("batched handles are not sharded"); return CF_INVALID_INPUT_ERROR; }
     if (!h || nranks < 1 || rank < 0 || rank >= nranks) { set_error("bad shard %d of %d", rank, nranks); return CF_INVALID_INPUT_ERROR; }
     CF_TRY(use_device(h));
+    if (rank != h->rank || nranks != h->nranks) {
+        h->win_f = -1.0;           // windows cover the shard only
+        peer_detach(h);            // the peers' block layout changes
+    }
     h->rank = rank;
     h->nranks = nranks;
     compute_shard(h);
@@ -333,6 +344,8 @@ int32_t cf_lowess_reset_windows(cf_lowess* h)
 }
 
 int32_t cf_lowess_count(const cf_lowess* h) { return (h && h->init) ? h->n : 0; }
+
+int64_t cf_lowess_launch_count(const cf_lowess* h) { return h ? (int64_t)h->launches : 0; }
 
 }  // extern "C"
 

@@ -67,6 +67,22 @@ __device__ __forceinline__ double fit_value(double S0, double S1, double S2, dou
 }
 #endif
 
+// ---- peer-memory exchange (peer.cu): the robustness step's two collectives done
+// by the kernels themselves over NVLink peer stores instead of NCCL ------------
+constexpr int kMaxPeers = 8;
+struct PeerComm {                                   // one per rank, IPC-mapped by all peers
+    unsigned long long flag[2][kMaxPeers];          // [0] histogram rounds, [1] barriers: epoch per source rank
+    unsigned long long slots[2][kMaxPeers][kHistLen];  // [epoch parity][source rank] digit histograms
+    int error;                                      // set when a wait timed out
+};
+struct PeerPtrs {                                   // by-value kernel argument
+    PeerComm* comm[kMaxPeers];
+    double* rw[kMaxPeers];
+    double* ys[kMaxPeers];
+    double* res[kMaxPeers];
+    int rank, nranks;
+};
+
 // ---- per-point neighbourhood (0-based, inclusive) ----------------------------
 struct Windows {
     int32_t* nleft;   // slide result, :663-669
@@ -103,6 +119,7 @@ struct cf_lowess {
     unsigned long long* hist = nullptr;  // nseries x kHistLen counters
     cf::SelectState* sel = nullptr;      // nseries states
     int32_t sel_cap = 0;
+    int32_t* span = nullptr;             // nseries x {min lo9, max hi9} over the shard (windows.cu)
 
     // fit kernel: partial-moment scratch for the K-way window split, tuning knobs
     double* part = nullptr;
@@ -115,6 +132,12 @@ struct cf_lowess {
     double* tree = nullptr;
     size_t tree_bytes = 0;
     int method = 0;            // CF_METHOD_DIRECT / CF_METHOD_TREE / CF_METHOD_AUTO
+
+    // peer-memory exchange (peer.cu); comm is this rank's own block
+    cf::PeerComm* comm = nullptr;
+    cf::PeerPtrs peer = {};
+    bool peer_attached = false;
+    unsigned long long epoch_hist = 0, epoch_bar = 0;
 
     // counters for cf_stats
     int launches = 0, fit_launches = 0;
@@ -132,6 +155,9 @@ int launch_select_reset(cf_lowess* h);
 int launch_hist(cf_lowess* h, int round);
 int launch_pick(cf_lowess* h, int round);
 int launch_bisquare(cf_lowess* h);
+int launch_peer_barrier(cf_lowess* h);        // peer.cu: all ranks reach this point
+int launch_peer_gather(cf_lowess* h);         // peer.cu: own ys/res block -> every rank
+void peer_detach(cf_lowess* h);               // peer.cu
 
 // device radix sort of (x, index) ascending, y co-permuted; d_perm may be null
 int sort_xy_device(const double* d_x_in, const double* d_y_in, int32_t n, double* d_x_out,

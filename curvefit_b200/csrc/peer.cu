@@ -1,0 +1,179 @@
+// peer.cu -- the two exchanges of a range-sharded robustness step done
+// by the kernels themselves over NVLink peer memory, not by NCCL:
+//
+//   * global median of |res| (src/curvefit_regression.f90:697-703): every select
+//     round, pick_kernel<true> (robust.cu) first stores this rank's digit histogram
+//     into slot [rank] of EVERY rank's PeerComm, raises its epoch flag there, waits
+//     for the flags of all ranks in its own PeerComm and sums the slots -- an
+//     all-reduce of 4096 integer counters fused into the scan that consumes it;
+//   * refreshed robustness weights (:704-713): bisquare_kernel<true> stores each
+//     weight of its block into every rank's rw vector (the all-gather that gives the
+//     neighbours their (ns-1)-point halo), followed by peer_barrier_kernel so that no
+//     rank starts the next fit pass before all blocks have landed;
+//   * peer_gather_kernel replicates the own block of ys / res the same way at the end.
+//
+// Memory is shared between the one-process-per-GPU ranks with CUDA IPC handles
+// (cf_lowess_peer_export / _attach; the host runtime moves the 64-byte handles, e.g.
+// with torch.distributed.all_gather).  Flags are monotone epochs, so a slot is reused
+// only two rounds later, after every rank has passed the round in between.  All waits
+// give up after kPeerTimeoutNs and set PeerComm::error instead of hanging the GPU.
+#include <string.h>
+
+#include "common.cuh"
+#include "peer.cuh"
+
+namespace cf {
+
+__global__ void __launch_bounds__(32)
+peer_barrier_kernel(const PeerPtrs pp, unsigned long long epoch)
+{
+    peer_signal_wait(pp, 1, epoch);
+}
+
+// own block [begin, end) of ys and res -> the same positions on every other rank
+__global__ void __launch_bounds__(256)
+peer_gather_kernel(const PeerPtrs pp, int32_t begin, int32_t end)
+{
+    const int32_t i = begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= end) return;
+    const double v = pp.ys[pp.rank][i], r = pp.res[pp.rank][i];
+#pragma unroll
+    for (int p = 0; p < kMaxPeers; ++p) {
+        if (p < pp.nranks && p != pp.rank) {
+            pp.ys[p][i] = v;
+            pp.res[p][i] = r;
+        }
+    }
+}
+
+int launch_peer_barrier(cf_lowess* h)
+{
+    if (!h->peer_attached) return CF_OK;
+    peer_barrier_kernel<<<1, 32, 0, h->stream>>>(h->peer, ++h->epoch_bar);
+    CF_CUDA(cudaGetLastError());
+    h->launches++;
+    return CF_OK;
+}
+
+int launch_peer_gather(cf_lowess* h)
+{
+    if (!h->peer_attached) { set_error("peers are not attached"); return CF_INVALID_INPUT_ERROR; }
+    const int cnt = h->end - h->begin;
+    if (cnt > 0) {
+        peer_gather_kernel<<<(cnt + 255) / 256, 256, 0, h->stream>>>(h->peer, h->begin, h->end);
+        CF_CUDA(cudaGetLastError());
+        h->launches++;
+    }
+    return launch_peer_barrier(h);
+}
+
+void peer_detach(cf_lowess* h)
+{
+    if (!h->peer_attached) return;
+    cudaStreamSynchronize(h->stream);
+    for (int p = 0; p < h->peer.nranks; ++p) {
+        if (p == h->peer.rank) continue;
+        if (h->peer.comm[p]) cudaIpcCloseMemHandle(h->peer.comm[p]);
+        if (h->peer.rw[p]) cudaIpcCloseMemHandle(h->peer.rw[p]);
+        if (h->peer.ys[p]) cudaIpcCloseMemHandle(h->peer.ys[p]);
+        if (h->peer.res[p]) cudaIpcCloseMemHandle(h->peer.res[p]);
+    }
+    h->peer = PeerPtrs{};
+    h->peer_attached = false;
+}
+
+}  // namespace cf
+
+using namespace cf;
+
+extern "C" {
+
+int32_t cf_lowess_peer_handle_bytes(void) { return 4 * (int32_t)sizeof(cudaIpcMemHandle_t); }
+
+int32_t cf_lowess_peer_export(cf_lowess* h, void* out)
+{
+    if (!h || !out) { set_error("null argument"); return CF_INVALID_INPUT_ERROR; }
+    if (!h->init || h->nseries != 1) { set_error("No data has been defined."); return CF_NO_DATA_DEFINED_ERROR; }
+    if (h->nranks > kMaxPeers) { set_error("at most %d ranks", kMaxPeers); return CF_INVALID_INPUT_ERROR; }
+    CF_CUDA(cudaSetDevice(h->device));
+    peer_detach(h);
+    if (!h->comm) CF_CUDA(cudaMalloc(&h->comm, sizeof(PeerComm)));
+    CF_CUDA(cudaMemsetAsync(h->comm, 0, sizeof(PeerComm), h->stream));
+    CF_CUDA(cudaStreamSynchronize(h->stream));
+    h->epoch_hist = h->epoch_bar = 0;
+    cudaIpcMemHandle_t hs[4];
+    CF_CUDA(cudaIpcGetMemHandle(&hs[0], h->comm));
+    CF_CUDA(cudaIpcGetMemHandle(&hs[1], h->rw));
+    CF_CUDA(cudaIpcGetMemHandle(&hs[2], h->ys));
+    CF_CUDA(cudaIpcGetMemHandle(&hs[3], h->res));
+    memcpy(out, hs, sizeof(hs));
+    return CF_OK;
+}
+
+int32_t cf_lowess_peer_attach(cf_lowess* h, const void* all_handles, int32_t nranks)
+{
+    if (!h || !all_handles) { set_error("null argument"); return CF_INVALID_INPUT_ERROR; }
+    if (nranks != h->nranks || nranks > kMaxPeers || !h->comm) {
+        set_error("peer_attach: %d ranks given, shard has %d (export first; at most %d)", (int)nranks,
+                  (int)h->nranks, kMaxPeers);
+        return CF_INVALID_INPUT_ERROR;
+    }
+    CF_CUDA(cudaSetDevice(h->device));
+    PeerPtrs pp = {};
+    pp.rank = h->rank;
+    pp.nranks = nranks;
+    const cudaIpcMemHandle_t* hs = static_cast<const cudaIpcMemHandle_t*>(all_handles);
+    int rc = CF_OK;
+    for (int p = 0; p < nranks && rc == CF_OK; ++p) {
+        if (p == h->rank) {
+            pp.comm[p] = h->comm; pp.rw[p] = h->rw; pp.ys[p] = h->ys; pp.res[p] = h->res;
+            continue;
+        }
+        void* ptr[4] = {nullptr, nullptr, nullptr, nullptr};
+        for (int k = 0; k < 4; ++k) {
+            cudaError_t e = cudaIpcOpenMemHandle(&ptr[k], hs[4 * p + k], cudaIpcMemLazyEnablePeerAccess);
+            if (e != cudaSuccess) { rc = cuda_fail(e, "cudaIpcOpenMemHandle", __FILE__, __LINE__); break; }
+        }
+        pp.comm[p] = static_cast<PeerComm*>(ptr[0]);
+        pp.rw[p] = static_cast<double*>(ptr[1]);
+        pp.ys[p] = static_cast<double*>(ptr[2]);
+        pp.res[p] = static_cast<double*>(ptr[3]);
+    }
+    h->peer = pp;
+    h->peer_attached = true;       // so that peer_detach closes what was opened
+    if (rc != CF_OK) peer_detach(h);
+    return rc;
+}
+
+int32_t cf_lowess_peer_detach(cf_lowess* h)
+{
+    if (!h) return CF_INVALID_INPUT_ERROR;
+    cudaSetDevice(h->device);
+    peer_detach(h);
+    return CF_OK;
+}
+
+int32_t cf_lowess_peer_attached(const cf_lowess* h) { return h && h->peer_attached ? 1 : 0; }
+
+int32_t cf_lowess_stage_gather(cf_lowess* h)
+{
+    if (!h || !h->init) return CF_NO_DATA_DEFINED_ERROR;
+    CF_CUDA(cudaSetDevice(h->device));
+    return launch_peer_gather(h);
+}
+
+int32_t cf_lowess_peer_error(cf_lowess* h, int32_t* flag)
+{
+    if (!h || !flag) return CF_INVALID_INPUT_ERROR;
+    *flag = 0;
+    if (!h->comm) return CF_OK;
+    CF_CUDA(cudaSetDevice(h->device));
+    int v = 0;
+    CF_CUDA(cudaMemcpyAsync(&v, &h->comm->error, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CF_CUDA(cudaStreamSynchronize(h->stream));
+    *flag = v;
+    if (v) set_error("a peer wait timed out (a rank did not reach the exchange)");
+    return CF_OK;
+}
+
+}  // extern "C"

@@ -8,6 +8,7 @@
 // All kernels work on the handle's shard [begin, end) of the sorted index range;
 // the digit histograms are the only data that must be summed across GPUs.
 #include "common.cuh"
+#include "peer.cuh"
 
 namespace cf {
 
@@ -119,12 +120,17 @@ int launch_hist(cf_lowess* h, int round)
 // One warp per tracked rank: locate the bin holding the rank, extend the prefix,
 // rebase the rank, clear the histogram for the next round; after the last round
 // form cmad, c1, c9 (:701-703).
-__global__ void __launch_bounds__(64)
-pick_kernel(SelectState* st, unsigned long long* hist, int round)
+// PEER: the histogram is first summed over the ranks through peer memory (peer.cuh).
+template <bool PEER>
+__global__ void __launch_bounds__(PEER ? 256 : 64)
+pick_kernel(SelectState* st, unsigned long long* hist, int round, const PeerPtrs pp,
+            unsigned long long epoch)
 {
     st += blockIdx.x;
     hist += (size_t)blockIdx.x * kHistLen;
+    if (PEER) peer_hist_allreduce(pp, hist, epoch);
     const int t = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (t < 2) {
     const int width = sel_width(round);
     const int bins = 1 << width;
     const int per = kSelBins / 32;
@@ -157,6 +163,7 @@ pick_kernel(SelectState* st, unsigned long long* hist, int round)
             cum += cnt;
         }
     }
+    }
     __syncthreads();
     for (int k = threadIdx.x; k < kHistLen; k += blockDim.x) hist[k] = 0ull;
     if (round == kSelRounds - 1 && threadIdx.x == 0) {
@@ -171,16 +178,22 @@ pick_kernel(SelectState* st, unsigned long long* hist, int round)
 
 int launch_pick(cf_lowess* h, int round)
 {
-    pick_kernel<<<h->nseries, 64, 0, h->stream>>>(h->sel, h->hist, round);
+    if (h->peer_attached)
+        pick_kernel<true><<<1, 256, 0, h->stream>>>(h->sel, h->hist, round, h->peer, ++h->epoch_hist);
+    else
+        pick_kernel<false><<<h->nseries, 64, 0, h->stream>>>(h->sel, h->hist, round, PeerPtrs{}, 0ull);
     CF_CUDA(cudaGetLastError());
     h->launches++;
     return CF_OK;
 }
 
 // ---- bisquare robustness weights (:704-713) ---------------------------------------------
+// PEER: the weight is stored into every rank's rw vector (the all-gather of the blocks).
+template <bool PEER>
 __global__ void __launch_bounds__(256)
 bisquare_kernel(const double* __restrict__ res, double* __restrict__ rw,
-                const SelectState* __restrict__ st, int32_t begin, int32_t end, int32_t n)
+                const SelectState* __restrict__ st, int32_t begin, int32_t end, int32_t n,
+                const PeerPtrs pp)
 {
     const int32_t i = begin + blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= end) return;
@@ -197,14 +210,26 @@ bisquare_kernel(const double* __restrict__ res, double* __restrict__ rw,
         w = __dmul_rn(u, u);
     }
     rw[i] = w;
+    if (PEER) {
+#pragma unroll
+        for (int p = 0; p < kMaxPeers; ++p)
+            if (p < pp.nranks && p != pp.rank) pp.rw[p][i] = w;
+    }
 }
 
 int launch_bisquare(cf_lowess* h)
 {
     const int cnt = h->end - h->begin;
-    if (cnt <= 0) return CF_OK;
-    bisquare_kernel<<<dim3((cnt + 255) / 256, h->nseries), 256, 0, h->stream>>>(
-        h->res, h->rw, h->sel, h->begin, h->end, h->n);
+    if (cnt <= 0) return launch_peer_barrier(h);   // an empty shard still meets the others
+    if (h->peer_attached) {
+        bisquare_kernel<true><<<(cnt + 255) / 256, 256, 0, h->stream>>>(
+            h->res, h->rw, h->sel, h->begin, h->end, h->n, h->peer);
+        CF_CUDA(cudaGetLastError());
+        h->launches++;
+        return launch_peer_barrier(h);      // every block has landed before the next fit pass
+    }
+    bisquare_kernel<false><<<dim3((cnt + 255) / 256, h->nseries), 256, 0, h->stream>>>(
+        h->res, h->rw, h->sel, h->begin, h->end, h->n, PeerPtrs{});
     CF_CUDA(cudaGetLastError());
     h->launches++;
     return CF_OK;

@@ -45,6 +45,7 @@ struct TreeParams {
     const double* rw;           // nullptr: all ones (first pass)
     double* ys;
     double* nodes;              // [series][total_nodes][kNodeLen]
+    const int32_t* span;        // [series]{min lo9, max hi9} over the shard's points (windows.cu)
     Windows w;
     int32_t n, ns, begin, end;
     int32_t nlevels;
@@ -68,6 +69,16 @@ __device__ __forceinline__ void node_span(int level, int64_t k, int32_t n, int32
     j1 = (int32_t)(b - 1);
 }
 
+// Only nodes that lie wholly inside the element span of the shard's windows can be
+// reached by tree_eval_kernel's walks (they tile sub-ranges of [lo9, hi9]); a parent
+// inside the span has both children inside it.  On a range-sharded series this keeps
+// the per-pass rebuild proportional to the shard plus its halo, not to n.
+__device__ __forceinline__ bool node_needed(const TreeParams& prm, int series, int32_t j0, int32_t j1)
+{
+    const int32_t lo = __ldg(prm.span + 2 * series), hi = __ldg(prm.span + 2 * series + 1);
+    return j0 >= lo && j1 <= hi;
+}
+
 // ---- build: leaves -------------------------------------------------------------------
 __global__ void __launch_bounds__(128)
 tree_leaf_kernel(const TreeParams prm)
@@ -82,6 +93,7 @@ tree_leaf_kernel(const TreeParams prm)
 
     int32_t j0, j1;
     node_span(0, leaf, prm.n, j0, j1);
+    if (!node_needed(prm, blockIdx.y, j0, j1)) return;
     const double xf = x[j0], xl = x[j1];
     const double c = 0.5 * xf + 0.5 * xl;
     const double d = 0.5 * (xl - xf);
@@ -137,12 +149,13 @@ __device__ __forceinline__ void shift_add(const double* src, double a, double b,
 }
 
 __device__ __forceinline__ void build_parent(const TreeParams& prm, const double* __restrict__ x,
-                                             double* base, int level, int32_t k)
+                                             double* base, int level, int32_t k, int series)
 {
     const double* ch = base + (prm.off[level - 1] + 2 * (int64_t)k) * kNodeLen;
     double* nd = base + (prm.off[level] + k) * kNodeLen;
     int32_t j0, j1;
     node_span(level, k, prm.n, j0, j1);
+    if (!node_needed(prm, series, j0, j1)) return;
     const double xf = x[j0], xl = x[j1];
     const double c = 0.5 * xf + 0.5 * xl;
     const double d = 0.5 * (xl - xf);
@@ -176,7 +189,7 @@ tree_merge_kernel(const TreeParams prm, int level)
     if (k >= prm.cnt[level]) return;
     const double* __restrict__ x = prm.x + (size_t)blockIdx.y * (size_t)prm.n;
     double* base = prm.nodes + (size_t)blockIdx.y * prm.total * kNodeLen;
-    build_parent(prm, x, base, level, k);
+    build_parent(prm, x, base, level, k, blockIdx.y);
 }
 
 // all levels from `level0` up in one CTA per series (they hold <= 2048 nodes)
@@ -187,7 +200,7 @@ tree_top_kernel(const TreeParams prm, int level0)
     double* base = prm.nodes + (size_t)blockIdx.x * prm.total * kNodeLen;
     for (int level = level0; level < prm.nlevels; ++level) {
         for (int32_t k = threadIdx.x; k < prm.cnt[level]; k += blockDim.x)
-            build_parent(prm, x, base, level, k);
+            build_parent(prm, x, base, level, k, blockIdx.x);
         __threadfence_block();
         __syncthreads();
     }
@@ -469,6 +482,7 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
         h->tree_bytes = need;
     }
     prm.nodes = h->tree;
+    prm.span = h->span;
 
     tree_leaf_kernel<<<dim3((prm.cnt[0] + 127) / 128, h->nseries), 128, 0, h->stream>>>(prm);
     CF_CUDA(cudaGetLastError());

@@ -12,11 +12,32 @@
 
 namespace cf {
 
+__device__ __forceinline__ void windows_point(const double* __restrict__ x, int32_t n, int32_t ns,
+                                              Windows w, int32_t i0, int32_t& out_l9, int32_t& out_r9);
+
 __global__ void __launch_bounds__(256)
-windows_kernel(const double* __restrict__ x, int32_t n, int32_t ns, Windows w)
+windows_kernel(const double* __restrict__ x, int32_t n, int32_t ns, Windows w, int32_t begin,
+               int32_t end, int32_t* __restrict__ span)
 {
-    const int32_t i0 = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i0 >= n) return;
+    // only the handle's shard [begin, end) of output points is searched; span[0..1]
+    // receives min lo9 / max hi9 over it (the elements its fits can touch)
+    const int32_t i0 = begin + blockIdx.x * blockDim.x + threadIdx.x;
+    const bool live = i0 < end;
+    int32_t l9 = INT32_MAX, r9 = -1;
+    if (live) windows_point(x, n, ns, w, i0, l9, r9);
+    l9 = __reduce_min_sync(0xffffffffu, l9);
+    r9 = __reduce_max_sync(0xffffffffu, r9);
+    if ((threadIdx.x & 31) == 0 && r9 >= 0) {
+        int32_t* sp = span + 2 * blockIdx.y;
+        atomicMin(&sp[0], l9);
+        atomicMax(&sp[1], r9);
+    }
+}
+
+
+__device__ __forceinline__ void windows_point(const double* __restrict__ x, int32_t n, int32_t ns,
+                                              Windows w, int32_t i0, int32_t& out_l9, int32_t& out_r9)
+{
     // batched mode: series blockIdx.y lives at offset blockIdx.y * n in every array;
     // all indices stay relative to the series
     const size_t off = (size_t)blockIdx.y * (size_t)n;
@@ -88,14 +109,26 @@ windows_kernel(const double* __restrict__ x, int32_t n, int32_t ns, Windows w)
     w.lo1[i0] = l1;
     w.hi1[i0] = r1;
     w.leader[i0] = i;
+    out_l9 = l9;
+    out_r9 = r9;
+}
+
+__global__ void span_init_kernel(int32_t* span, int32_t nseries)
+{
+    const int32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s < nseries) { span[2 * s] = INT32_MAX; span[2 * s + 1] = -1; }
 }
 
 int launch_windows(cf_lowess* h, int32_t ns)
 {
     if (h->n < 2) return CF_OK;
     const int threads = 256;
-    const int blocks = (h->n + threads - 1) / threads;
-    windows_kernel<<<dim3(blocks, h->nseries), threads, 0, h->stream>>>(h->x, h->n, ns, h->win);
+    const int cnt = h->end - h->begin;
+    span_init_kernel<<<(h->nseries + 255) / 256, 256, 0, h->stream>>>(h->span, h->nseries);
+    if (cnt <= 0) return CF_OK;
+    const int blocks = (cnt + threads - 1) / threads;
+    windows_kernel<<<dim3(blocks, h->nseries), threads, 0, h->stream>>>(h->x, h->n, ns, h->win, h->begin,
+                                                                        h->end, h->span);
     CF_CUDA(cudaGetLastError());
     h->launches++;
     return CF_OK;

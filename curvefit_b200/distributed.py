@@ -8,8 +8,12 @@ per point) and the whole robustness-weight vector, fits only its own block
     (src/curvefit_regression.f90:697-703 -- the reference's full sort);
   * its block of new robustness weights (all-gather) -- the superset of the
     (ns-1)-point halo the neighbours need for :551.
-torch.distributed is the plumbing (NCCL on GPUs, gloo in the CPU tests); the
-device stages are libcurvefit_cuda's cf_lowess_stage_* entry points.  Per-point
+Two transports: "p2p" (default on GPUs) -- the kernels do both exchanges
+themselves through NVLink peer memory (csrc/peer.cu: histogram all-reduce fused
+into the select scan, weights stored straight into every rank's vector, device
+barriers; torch.distributed only carries the CUDA IPC handles once) -- and "nccl"
+(torch.distributed collectives between the stages; also what the gloo CPU tests
+exercise).  The device stages are libcurvefit_cuda's cf_lowess_stage_* entry points.  Per-point
 sums never cross ranks, so ys is bit-identical for any number of ranks.
 """
 from __future__ import annotations
@@ -79,6 +83,61 @@ class DeviceStages:
         self.cmad = torch.as_tensor(_DevArray(buf(_lib.CF_BUF_CMAD), 3, "<f8"), device=dev)
         self.rounds = self.lib.cf_lowess_select_rounds()
         self.launches = 0
+        self.p2p = False
+
+    def attach_peers(self, group: Optional[dist.ProcessGroup] = None) -> bool:
+        """Map every rank's exchange block, rw, ys and res into this process (CUDA IPC)
+        so that the stages exchange through peer memory.  Collective.  Returns False
+        (and leaves the NCCL transport in place) if any rank could not attach."""
+        if self.nranks == 1:
+            return False
+        nb = self.lib.cf_lowess_peer_handle_bytes()
+        mine = (C.c_uint8 * nb)()
+        rc = self.lib.cf_lowess_peer_export(self.h, mine)
+        dev = torch.device("cuda", torch.cuda.current_device())
+        own = torch.frombuffer(bytearray(bytes(mine)), dtype=torch.uint8).to(dev)
+        allh = torch.empty(nb * self.nranks, dtype=torch.uint8, device=dev)
+        dist.all_gather_into_tensor(allh, own, group=group)
+        if rc == 0:
+            blob = bytes(allh.cpu().numpy().tobytes())
+            rc = self.lib.cf_lowess_peer_attach(self.h, blob, self.nranks)
+        ok = torch.tensor([1 if rc == 0 else 0], device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)      # also the post-attach barrier
+        torch.cuda.synchronize()
+        self.p2p = bool(ok.item() == 1)
+        if not self.p2p:
+            self.lib.cf_lowess_peer_detach(self.h)
+        return self.p2p
+
+    def detach_peers(self, group: Optional[dist.ProcessGroup] = None) -> None:
+        """Collective: no rank unmaps while a peer may still store, and no rank frees
+        its buffers (re-init, close) while a peer still has them mapped."""
+        if not self.p2p:
+            return
+        torch.cuda.synchronize()
+        dist.barrier(group=group)
+        self.lib.cf_lowess_peer_detach(self.h)
+        self.p2p = False
+        dist.barrier(group=group)
+
+    def upload(self, x: np.ndarray, y: np.ndarray) -> None:
+        """ls_init with srt = .false. on the existing handle (buffers stay in place when n
+        is unchanged, so peer mappings and the tensor views above remain valid)."""
+        assert x.size == self.n and y.size == self.n, "series length is fixed for a sharded handle"
+        self._check(self.lib.cf_lowess_init(self.h, x.ctypes.data_as(_lib.c_dp), y.ctypes.data_as(_lib.c_dp),
+                                            self.n, 0))
+
+    def fetch(self, ys, rw, res) -> None:
+        p = lambda a: None if a is None else a.ctypes.data_as(_lib.c_dp)
+        self._check(self.lib.cf_lowess_fetch(self.h, p(ys), p(rw), p(res)))
+
+    def gather(self) -> None:
+        self._check(self.lib.cf_lowess_stage_gather(self.h))
+
+    def peer_error(self) -> bool:
+        flag = C.c_int32(0)
+        self._check(self.lib.cf_lowess_peer_error(self.h, C.byref(flag)))
+        return flag.value != 0
 
     def _check(self, rc: int) -> None:
         if rc != 0:
@@ -115,7 +174,7 @@ class ShardedLowess:
 
     def run(self, f: float, nsteps: int = 2, gather: bool = True):
         s = self.s
-        multi = s.nranks > 1
+        multi = s.nranks > 1 and not getattr(s, "p2p", False)   # p2p: the kernels exchange
         s.begin_run(f)
         for p in range(nsteps + 1):                           # :657
             s.fit_pass(p > 0)                                 # :662-695 on the block
@@ -136,10 +195,27 @@ class ShardedLowess:
             return None
         return self.gather_results()
 
+    def smooth_host(self, x: np.ndarray, y: np.ndarray, f: float, nsteps: int = 2, out=None):
+        """smooth() with HOST buffers on every call: each rank uploads the (sorted) series,
+        the ranks smooth it together, and the caller's rank(s) read ys, rw, res back.
+        `out` = (ys, rw, res) host arrays of length n, or None on ranks that do not need
+        the result.  The series length must not change while peers are attached."""
+        s = self.s
+        s.upload(x, y)
+        self.run(f, nsteps, gather=True)
+        if out is not None:
+            s.fetch(*out)
+        else:
+            s.sync()
+        return out
+
     def gather_results(self):
         """Full-length ys and res on every rank (block-padded all-gather)."""
         s = self.s
         if s.nranks == 1:
+            return s.ys[: s.n], s.res[: s.n]
+        if getattr(s, "p2p", False):
+            s.gather()            # own block stored into every rank's ys / res + device barrier
             return s.ys[: s.n], s.res[: s.n]
         outs = []
         for src in (s.ys, s.res):

@@ -165,6 +165,8 @@ CF_API int32_t cf_lowess_fetch(cf_lowess* h, double* ys, double* rw, double* res
 /* Sorted x / y (what get_x / get_y index, :893-920). */
 CF_API int32_t cf_lowess_fetch_xy(cf_lowess* h, double* x_sorted, double* y_sorted);
 CF_API int32_t cf_lowess_count(const cf_lowess* h);  /* get_count, :876-884 */
+/* Kernels of this library launched through the handle since it was created. */
+CF_API int64_t cf_lowess_launch_count(const cf_lowess* h);
 
 /* Neighbourhoods for span fraction f, 1-based, each array length n or NULL:
  * nleft/nright as the slide loop leaves them (:663-669); lo9/hi9 = first/last
@@ -188,6 +190,30 @@ CF_API int32_t cf_lowess_stage_pick(cf_lowess* h, int32_t round);    /* scan (po
 CF_API int32_t cf_lowess_stage_weights(cf_lowess* h);                /* bisquare, shard  */
 CF_API int32_t cf_lowess_select_rounds(void);
 CF_API int32_t cf_lowess_sync(cf_lowess* h);
+
+/* ------------------------------------------------------------------------
+ * Peer-memory exchange (NVLink / NVSwitch; one process per GPU of one box).
+ * Once attached, the robustness step of a range-sharded series needs no host
+ * collective: cf_lowess_stage_pick sums the |res| digit histograms of all ranks
+ * through peer stores inside the kernel that scans them (the global median,
+ * :697-703), cf_lowess_stage_weights stores each new robustness weight into every
+ * rank's vector (:704-713; the halo the neighbours' next pass needs) and ends
+ * with a device-side barrier, cf_lowess_stage_gather replicates ys / res.
+ *   1. every rank: cf_lowess_init, cf_lowess_set_shard, cf_lowess_peer_export
+ *      -> cf_lowess_peer_handle_bytes() bytes of CUDA IPC handles;
+ *   2. the host runtime all-gathers them (rank-major) and every rank calls
+ *      cf_lowess_peer_attach, then synchronises with the others once;
+ *   3. all ranks issue the same sequence of stage calls.
+ * A rank that never arrives does not hang the others: waits give up after 4 s
+ * and cf_lowess_peer_error reports it.  init / set_shard detach.  At most 8 ranks.
+ * ---------------------------------------------------------------------- */
+CF_API int32_t cf_lowess_peer_handle_bytes(void);
+CF_API int32_t cf_lowess_peer_export(cf_lowess* h, void* handles_out);
+CF_API int32_t cf_lowess_peer_attach(cf_lowess* h, const void* all_handles, int32_t nranks);
+CF_API int32_t cf_lowess_peer_detach(cf_lowess* h);
+CF_API int32_t cf_lowess_peer_attached(const cf_lowess* h);
+CF_API int32_t cf_lowess_peer_error(cf_lowess* h, int32_t* flag);
+CF_API int32_t cf_lowess_stage_gather(cf_lowess* h);   /* own ys/res block -> all ranks */
 
 /* Device pointers of the handle's buffers, for zero-copy wrapping by the host
  * runtime (e.g. as torch tensors for NCCL collectives). */

@@ -23,38 +23,49 @@ def main():
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     ok = True
-    for n, f, nsteps, kind in [(50_000, 0.1, 3, "random"), (200_000, 0.05, 2, "grid"), (3000, 0.3, 2, "ties")]:
-        if kind == "grid":
-            x = datagen.grid_x(n)
-        elif kind == "ties":
-            x = np.sort(np.round(datagen.random_x(n, 5) * 400) / 400)
-        else:
-            x = np.sort(datagen.random_x(n, 3))
-        y = datagen.noisy_y(x, 3)
-        stream = torch_stream_handle()
-        solo = lowess_smoothing(device=local)
-        solo.initialize(x, y, srt=False)
-        ys_ref = solo.smooth(f, nsteps=nsteps)
-        rw_ref, res_ref = solo.m_weights.copy(), solo.m_residuals.copy()
+    cases = [(50_000, 0.1, 3, "random"), (200_000, 0.05, 2, "grid"), (3000, 0.3, 2, "ties"),
+             (300_000, 0.2, 3, "random")]
+    for transport, method in [("nccl", "direct"), ("p2p", "direct"), ("p2p", "tree")]:
+      for n, f, nsteps, kind in cases:
+          if kind == "grid":
+              x = datagen.grid_x(n)
+          elif kind == "ties":
+              x = np.sort(np.round(datagen.random_x(n, 5) * 400) / 400)
+          else:
+              x = np.sort(datagen.random_x(n, 3))
+          y = datagen.noisy_y(x, 3)
+          stream = torch_stream_handle()
+          solo = lowess_smoothing(device=local)
+          solo.set_method(method)
+          solo.initialize(x, y, srt=False)
+          ys_ref = solo.smooth(f, nsteps=nsteps)
+          rw_ref, res_ref = solo.m_weights.copy(), solo.m_residuals.copy()
 
-        fit = lowess_smoothing(device=local, stream=stream)
-        fit.initialize(x, y, srt=False)
-        job = ShardedLowess(DeviceStages(fit, rank, world))
-        ys, res = job.run(f, nsteps)
-        torch.cuda.synchronize()
-        ys, res = ys.cpu().numpy(), res.cpu().numpy()
-        rw = job.s.rw[:n].cpu().numpy()
-        cmad = job.s.cmad.cpu().numpy()[0]
-        scale = np.max(np.abs(ys_ref))
-        d_ys = np.max(np.abs(ys - ys_ref)) / scale
-        d_rw = np.max(np.abs(rw - rw_ref))
-        d_res = np.max(np.abs(res - res_ref)) / scale
-        d_c = abs(cmad - solo.last_stats.cmad_last) / solo.last_stats.cmad_last
-        good = d_ys <= 1e-12 and d_rw <= 1e-9 and d_res <= 1e-12 and d_c <= 1e-12
-        ok &= bool(good)
-        print(f"[rank {rank}/{world}] n={n} f={f} nsteps={nsteps} {kind}: |dys|={d_ys:.2e} |drw|={d_rw:.2e} "
-              f"|dres|={d_res:.2e} dcmad={d_c:.2e} bitwise_ys={np.array_equal(ys, ys_ref)} "
-              f"collectives={job.collectives} {'OK' if good else 'FAIL'}", flush=True)
+          fit = lowess_smoothing(device=local, stream=stream)
+          fit.set_method(method)
+          fit.initialize(x, y, srt=False)
+          stages = DeviceStages(fit, rank, world)
+          if transport == "p2p":
+              assert stages.attach_peers(), "peer attach failed"
+          job = ShardedLowess(stages)
+          ys, res = job.run(f, nsteps)
+          torch.cuda.synchronize()
+          ys, res = ys.cpu().numpy(), res.cpu().numpy()
+          rw = job.s.rw[:n].cpu().numpy()
+          cmad = job.s.cmad.cpu().numpy()[0]
+          scale = np.max(np.abs(ys_ref))
+          d_ys = np.max(np.abs(ys - ys_ref)) / scale
+          d_rw = np.max(np.abs(rw - rw_ref))
+          d_res = np.max(np.abs(res - res_ref)) / scale
+          d_c = abs(cmad - solo.last_stats.cmad_last) / solo.last_stats.cmad_last
+          perr = stages.peer_error() if transport == "p2p" else False
+          good = d_ys <= 1e-12 and d_rw <= 1e-9 and d_res <= 1e-12 and d_c <= 1e-12 and not perr
+          ok &= bool(good)
+          print(f"[rank {rank}/{world}] {transport}/{method} n={n} f={f} nsteps={nsteps} {kind}: |dys|={d_ys:.2e} |drw|={d_rw:.2e} "
+                f"|dres|={d_res:.2e} dcmad={d_c:.2e} bitwise_ys={np.array_equal(ys, ys_ref)} "
+                f"collectives={job.collectives} {'OK' if good else 'FAIL'}", flush=True)
+          stages.detach_peers()     # collective; before any rank frees its buffers
+          del job, stages, fit, solo
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     dist.destroy_process_group()
