@@ -68,13 +68,14 @@ SIGNATURES = {
     "cf_lowess_peer_detach": (C.c_int32, [C.c_void_p]),
     "cf_lowess_peer_attached": (C.c_int32, [C.c_void_p]),
     "cf_lowess_peer_error": (C.c_int32, [C.c_void_p, c_ip]),
-    "cf_lowess_stage_gather": (C.c_int32, [C.c_void_p]),
+    "cf_lowess_stage_gather": (C.c_int32, [C.c_void_p, C.c_int32]),
     "cf_lowess_sync": (C.c_int32, [C.c_void_p]),
     "cf_lowess_buffer": (C.c_void_p, [C.c_void_p, C.c_int32]),
     "cf_lowess_hist_len": (C.c_int32, []),
     "cf_fp64_peak": (C.c_int32, [C.c_int32, C.c_double, c_dp, c_dp]),
 }
 
+CF_GATHER_YS, CF_GATHER_RES, CF_GATHER_RW = 1, 2, 4
 CF_METHOD_DIRECT, CF_METHOD_TREE, CF_METHOD_AUTO = range(3)
 CF_BUF_X, CF_BUF_Y, CF_BUF_YS, CF_BUF_RW, CF_BUF_RES, CF_BUF_HIST, CF_BUF_CMAD = range(7)
 

@@ -407,6 +407,7 @@ int32_t cf_lowess_run(cf_lowess* h, double f, int32_t nsteps, cf_stats* st)
     const int l0 = h->launches, f0 = h->fit_launches;
     CF_CUDA(cudaEventRecord(h->ev[0], h->stream));
     CF_TRY(begin_stage(h, f));
+    if (h->n >= 2) CF_TRY(launch_peer_spans(h));    // attached handles: all ranks call run together
     CF_CUDA(cudaEventRecord(h->ev[1], h->stream));
     if (h->n < 2) {                                                 // :651-654
         if (h->n == 1) CF_CUDA(cudaMemcpyAsync(h->ys, h->y, sizeof(double) * (size_t)h->nseries, cudaMemcpyDeviceToDevice, h->stream));
@@ -439,6 +440,7 @@ int32_t cf_lowess_run_from_rw(cf_lowess* h, double f, const double* rw_in, int32
     CF_TRY(use_device(h));
     CF_TRY(begin_stage(h, f));
     if (h->n < 2) { set_error("n < 2"); return CF_INVALID_INPUT_ERROR; }
+    CF_TRY(launch_peer_spans(h));
     if (rw_in)
         CF_CUDA(cudaMemcpyAsync(h->rw, rw_in, sizeof(double) * (size_t)h->n, cudaMemcpyHostToDevice, h->stream));
     return run_passes(h, passes, rw_in != nullptr, nullptr);
@@ -509,6 +511,7 @@ int32_t cf_lowess_stage_begin(cf_lowess* h, double f)
     CF_TRY(use_device(h));
     CF_TRY(begin_stage(h, f));
     if (h->n < 2) { set_error("n < 2"); return CF_INVALID_INPUT_ERROR; }
+    CF_TRY(launch_peer_spans(h));        // attached: every rank learns whose windows reach what
     return launch_select_reset(h);
 }
 int32_t cf_lowess_stage_fit(cf_lowess* h, int32_t use_rw)

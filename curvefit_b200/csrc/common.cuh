@@ -74,6 +74,8 @@ struct PeerComm {                                   // one per rank, IPC-mapped 
     unsigned long long flag[2][kMaxPeers];          // [0] histogram rounds, [1] barriers: epoch per source rank
     unsigned long long slots[2][kMaxPeers][kHistLen];  // [epoch parity][source rank] digit histograms
     int error;                                      // set when a wait timed out
+    int32_t span[2];                                // this rank's element span (windows.cu), published
+    int32_t peer_span[kMaxPeers][2];                // every rank's span, local copy made after the barrier
 };
 struct PeerPtrs {                                   // by-value kernel argument
     PeerComm* comm[kMaxPeers];
@@ -156,7 +158,8 @@ int launch_hist(cf_lowess* h, int round);
 int launch_pick(cf_lowess* h, int round);
 int launch_bisquare(cf_lowess* h);
 int launch_peer_barrier(cf_lowess* h);        // peer.cu: all ranks reach this point
-int launch_peer_gather(cf_lowess* h);         // peer.cu: own ys/res block -> every rank
+int launch_peer_gather(cf_lowess* h, int what);  // peer.cu: own ys/res/rw block -> every rank
+int launch_peer_spans(cf_lowess* h);          // peer.cu: publish the shard's element span, learn the peers'
 void peer_detach(cf_lowess* h);               // peer.cu
 
 // device radix sort of (x, index) ascending, y co-permuted; d_perm may be null

@@ -7,10 +7,13 @@
 //     for the flags of all ranks in its own PeerComm and sums the slots -- an
 //     all-reduce of 4096 integer counters fused into the scan that consumes it;
 //   * refreshed robustness weights (:704-713): bisquare_kernel<true> stores each
-//     weight of its block into every rank's rw vector (the all-gather that gives the
-//     neighbours their (ns-1)-point halo), followed by peer_barrier_kernel so that no
-//     rank starts the next fit pass before all blocks have landed;
-//   * peer_gather_kernel replicates the own block of ys / res the same way at the end.
+//     weight of its block into the rw vector of every rank whose windows can reach
+//     it -- the (ns-1)-point HALO exchange: each rank publishes the element span
+//     [min lo9, max hi9] of its shard's windows once per smooth (peer_spans_kernel) --
+//     followed by peer_barrier_kernel so that no rank starts the next fit pass before
+//     its halo has landed;
+//   * peer_gather_kernel replicates the own block of ys / res / rw on every rank at
+//     the end (the full-length result of smooth()).
 //
 // Memory is shared between the one-process-per-GPU ranks with CUDA IPC handles
 // (cf_lowess_peer_export / _attach; the host runtime moves the 64-byte handles, e.g.
@@ -30,18 +33,40 @@ peer_barrier_kernel(const PeerPtrs pp, unsigned long long epoch)
     peer_signal_wait(pp, 1, epoch);
 }
 
-// own block [begin, end) of ys and res -> the same positions on every other rank
+// Publishes this rank's element span, meets the other ranks, copies their spans.
+__global__ void __launch_bounds__(32)
+peer_spans_kernel(const PeerPtrs pp, const int32_t* __restrict__ span, unsigned long long epoch)
+{
+    PeerComm* own = pp.comm[pp.rank];
+    if (threadIdx.x == 0) {
+        own->span[0] = span[0];
+        own->span[1] = span[1];
+    }
+    __threadfence_system();
+    __syncwarp();
+    peer_signal_wait(pp, 1, epoch);
+    const int p = threadIdx.x;
+    if (p < pp.nranks) {
+        const volatile int32_t* theirs = pp.comm[p]->span;
+        own->peer_span[p][0] = theirs[0];
+        own->peer_span[p][1] = theirs[1];
+    }
+}
+
+// own block [begin, end) of ys / res / rw (bits 0 / 1 / 2 of `what`) -> the same
+// positions on every other rank
 __global__ void __launch_bounds__(256)
-peer_gather_kernel(const PeerPtrs pp, int32_t begin, int32_t end)
+peer_gather_kernel(const PeerPtrs pp, int32_t begin, int32_t end, int what)
 {
     const int32_t i = begin + blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= end) return;
-    const double v = pp.ys[pp.rank][i], r = pp.res[pp.rank][i];
+    const double v = pp.ys[pp.rank][i], r = pp.res[pp.rank][i], w = pp.rw[pp.rank][i];
 #pragma unroll
     for (int p = 0; p < kMaxPeers; ++p) {
         if (p < pp.nranks && p != pp.rank) {
-            pp.ys[p][i] = v;
-            pp.res[p][i] = r;
+            if (what & 1) pp.ys[p][i] = v;
+            if (what & 2) pp.res[p][i] = r;
+            if (what & 4) pp.rw[p][i] = w;
         }
     }
 }
@@ -55,12 +80,21 @@ int launch_peer_barrier(cf_lowess* h)
     return CF_OK;
 }
 
-int launch_peer_gather(cf_lowess* h)
+int launch_peer_spans(cf_lowess* h)
+{
+    if (!h->peer_attached) return CF_OK;
+    peer_spans_kernel<<<1, 32, 0, h->stream>>>(h->peer, h->span, ++h->epoch_bar);
+    CF_CUDA(cudaGetLastError());
+    h->launches++;
+    return CF_OK;
+}
+
+int launch_peer_gather(cf_lowess* h, int what)
 {
     if (!h->peer_attached) { set_error("peers are not attached"); return CF_INVALID_INPUT_ERROR; }
     const int cnt = h->end - h->begin;
-    if (cnt > 0) {
-        peer_gather_kernel<<<(cnt + 255) / 256, 256, 0, h->stream>>>(h->peer, h->begin, h->end);
+    if (cnt > 0 && (what & 7)) {
+        peer_gather_kernel<<<(cnt + 255) / 256, 256, 0, h->stream>>>(h->peer, h->begin, h->end, what);
         CF_CUDA(cudaGetLastError());
         h->launches++;
     }
@@ -155,11 +189,11 @@ int32_t cf_lowess_peer_detach(cf_lowess* h)
 
 int32_t cf_lowess_peer_attached(const cf_lowess* h) { return h && h->peer_attached ? 1 : 0; }
 
-int32_t cf_lowess_stage_gather(cf_lowess* h)
+int32_t cf_lowess_stage_gather(cf_lowess* h, int32_t what)
 {
     if (!h || !h->init) return CF_NO_DATA_DEFINED_ERROR;
     CF_CUDA(cudaSetDevice(h->device));
-    return launch_peer_gather(h);
+    return launch_peer_gather(h, what);
 }
 
 int32_t cf_lowess_peer_error(cf_lowess* h, int32_t* flag)

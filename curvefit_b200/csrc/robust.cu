@@ -188,7 +188,7 @@ int launch_pick(cf_lowess* h, int round)
 }
 
 // ---- bisquare robustness weights (:704-713) ---------------------------------------------
-// PEER: the weight is stored into every rank's rw vector (the all-gather of the blocks).
+// PEER: the weight is also stored into the rw vector of every rank that needs it.
 template <bool PEER>
 __global__ void __launch_bounds__(256)
 bisquare_kernel(const double* __restrict__ res, double* __restrict__ rw,
@@ -211,9 +211,12 @@ bisquare_kernel(const double* __restrict__ res, double* __restrict__ rw,
     }
     rw[i] = w;
     if (PEER) {
+        // halo exchange: only ranks whose windows reach element i get it
+        const PeerComm* own = pp.comm[pp.rank];
 #pragma unroll
         for (int p = 0; p < kMaxPeers; ++p)
-            if (p < pp.nranks && p != pp.rank) pp.rw[p][i] = w;
+            if (p < pp.nranks && p != pp.rank && i >= own->peer_span[p][0] && i <= own->peer_span[p][1])
+                pp.rw[p][i] = w;
     }
 }
 

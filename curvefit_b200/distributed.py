@@ -131,8 +131,8 @@ class DeviceStages:
         p = lambda a: None if a is None else a.ctypes.data_as(_lib.c_dp)
         self._check(self.lib.cf_lowess_fetch(self.h, p(ys), p(rw), p(res)))
 
-    def gather(self) -> None:
-        self._check(self.lib.cf_lowess_stage_gather(self.h))
+    def gather(self, what: int = _lib.CF_GATHER_YS | _lib.CF_GATHER_RES) -> None:
+        self._check(self.lib.cf_lowess_stage_gather(self.h, what))
 
     def peer_error(self) -> bool:
         flag = C.c_int32(0)
@@ -172,7 +172,7 @@ class ShardedLowess:
         self.group = group
         self.collectives = 0
 
-    def run(self, f: float, nsteps: int = 2, gather: bool = True):
+    def run(self, f: float, nsteps: int = 2, gather: bool = True, with_rw: bool = False):
         s = self.s
         multi = s.nranks > 1 and not getattr(s, "p2p", False)   # p2p: the kernels exchange
         s.begin_run(f)
@@ -193,7 +193,7 @@ class ShardedLowess:
                 self.collectives += 1
         if not gather:
             return None
-        return self.gather_results()
+        return self.gather_results(with_rw)
 
     def smooth_host(self, x: np.ndarray, y: np.ndarray, f: float, nsteps: int = 2, out=None):
         """smooth() with HOST buffers on every call: each rank uploads the (sorted) series,
@@ -202,20 +202,23 @@ class ShardedLowess:
         the result.  The series length must not change while peers are attached."""
         s = self.s
         s.upload(x, y)
-        self.run(f, nsteps, gather=True)
+        self.run(f, nsteps, gather=True, with_rw=True)
         if out is not None:
             s.fetch(*out)
         else:
             s.sync()
         return out
 
-    def gather_results(self):
-        """Full-length ys and res on every rank (block-padded all-gather)."""
+    def gather_results(self, with_rw: bool = False):
+        """Full-length ys and res on every rank (block-padded all-gather).  with_rw: the
+        p2p transport delivers only halo weights during the run, so the full-length
+        m_weights vector is completed here when the caller wants it."""
         s = self.s
         if s.nranks == 1:
             return s.ys[: s.n], s.res[: s.n]
         if getattr(s, "p2p", False):
-            s.gather()            # own block stored into every rank's ys / res + device barrier
+            # own block stored into every rank's ys / res (/ rw) + device barrier
+            s.gather(_lib.CF_GATHER_YS | _lib.CF_GATHER_RES | (_lib.CF_GATHER_RW if with_rw else 0))
             return s.ys[: s.n], s.res[: s.n]
         outs = []
         for src in (s.ys, s.res):

@@ -196,9 +196,11 @@ CF_API int32_t cf_lowess_sync(cf_lowess* h);
  * Once attached, the robustness step of a range-sharded series needs no host
  * collective: cf_lowess_stage_pick sums the |res| digit histograms of all ranks
  * through peer stores inside the kernel that scans them (the global median,
- * :697-703), cf_lowess_stage_weights stores each new robustness weight into every
- * rank's vector (:704-713; the halo the neighbours' next pass needs) and ends
- * with a device-side barrier, cf_lowess_stage_gather replicates ys / res.
+ * :697-703), cf_lowess_stage_weights stores each new robustness weight into the
+ * vector of every rank whose windows reach it (:704-713; the (ns-1)-point halo
+ * exchange) and ends with a device-side barrier, cf_lowess_stage_gather
+ * replicates the results.  Every call that runs passes on an attached handle
+ * (the stage calls, cf_lowess_run) is collective: all ranks must make it.
  *   1. every rank: cf_lowess_init, cf_lowess_set_shard, cf_lowess_peer_export
  *      -> cf_lowess_peer_handle_bytes() bytes of CUDA IPC handles;
  *   2. the host runtime all-gathers them (rank-major) and every rank calls
@@ -213,7 +215,12 @@ CF_API int32_t cf_lowess_peer_attach(cf_lowess* h, const void* all_handles, int3
 CF_API int32_t cf_lowess_peer_detach(cf_lowess* h);
 CF_API int32_t cf_lowess_peer_attached(const cf_lowess* h);
 CF_API int32_t cf_lowess_peer_error(cf_lowess* h, int32_t* flag);
-CF_API int32_t cf_lowess_stage_gather(cf_lowess* h);   /* own ys/res block -> all ranks */
+/* Replicate the own block of ys (CF_GATHER_YS), res (CF_GATHER_RES), rw (CF_GATHER_RW;
+ * during the run a rank receives only the weights its windows reach) on all ranks. */
+#define CF_GATHER_YS 1
+#define CF_GATHER_RES 2
+#define CF_GATHER_RW 4
+CF_API int32_t cf_lowess_stage_gather(cf_lowess* h, int32_t what);
 
 /* Device pointers of the handle's buffers, for zero-copy wrapping by the host
  * runtime (e.g. as torch tensors for NCCL collectives). */

@@ -48,7 +48,7 @@ def main():
           if transport == "p2p":
               assert stages.attach_peers(), "peer attach failed"
           job = ShardedLowess(stages)
-          ys, res = job.run(f, nsteps)
+          ys, res = job.run(f, nsteps, with_rw=True)
           torch.cuda.synchronize()
           ys, res = ys.cpu().numpy(), res.cpu().numpy()
           rw = job.s.rw[:n].cpu().numpy()
