@@ -37,6 +37,11 @@ SIGNATURES = {
     "cf_lowess_span": (C.c_int32, [C.c_int32, C.c_double]),
     "cf_sort_xy": (C.c_int32, [c_dp, c_dp, C.c_int32, c_dp, c_dp, c_ip]),
     "cf_lowess_smooth": (C.c_int32, [c_dp, c_dp, C.c_int32, C.c_double, C.c_int32, c_dp, c_dp, c_dp]),
+    "cf_lowess_smooth_delta": (C.c_int32, [c_dp, c_dp, C.c_int32, C.c_double, C.c_int32, C.c_double,
+                                           c_dp, c_dp, c_dp]),
+    "cf_lowess_set_delta": (C.c_int32, [C.c_void_p, C.c_double]),
+    "cf_lowess_delta": (C.c_double, [C.c_void_p]),
+    "cf_lowess_fitted": (C.c_int32, [C.c_void_p, c_ip, c_ip, C.c_int32]),
     "cf_lowess_smooth_batched": (C.c_int32, [c_dp, c_dp, C.c_int32, C.c_int32, C.c_double, C.c_int32,
                                              c_dp, c_dp, c_dp]),
     "cf_lowess_create": (C.c_int32, [C.POINTER(C.c_void_p), C.c_int32, C.c_void_p]),

@@ -130,6 +130,10 @@ static int begin_stage(cf_lowess* h, double f)
     if (!h->init) { set_error("No data has been defined."); return CF_NO_DATA_DEFINED_ERROR; }
     if (!(f == f)) { set_error("f is NaN"); return CF_INVALID_INPUT_ERROR; }
     const int32_t ns = cf_lowess_span(h->n, f);
+    if (h->n >= 2 && h->delta > 0.0 && h->delta_built != h->delta) {
+        CF_TRY(delta_prepare(h));          // fitted-point list (src/curvefit_regression.f90:681-690)
+        h->win_f = -1.0;                   // windows are per fitted point
+    }
     if (h->n >= 2 && (h->win_f != f || h->ns != ns)) {
         h->ns = ns;
         CF_TRY(launch_windows(h, ns));
@@ -228,6 +232,7 @@ void cf_lowess_destroy(cf_lowess* h)
     cudaFree(h->span);
     cudaFree(h->part);
     cudaFree(h->tree);
+    delta_free(h);
     for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -241,6 +246,7 @@ static int32_t init_common(cf_lowess* h, const void* x, const void* y, int32_t n
     CF_TRY(use_device(h));
     h->init = false;                                   // :758
     h->win_f = -1.0;
+    h->delta_built = -1.0;
     h->nseries = 1;
     CF_TRY(reserve(h, n));
     h->n = n;
@@ -335,6 +341,41 @@ int32_t cf_lowess_set_method(cf_lowess* h, int32_t method)
 }
 
 int32_t cf_lowess_method(const cf_lowess* h) { return h ? h->method : -1; }
+
+int32_t cf_lowess_set_delta(cf_lowess* h, double delta)
+{
+    if (!h || !(delta >= 0.0) || !(delta <= 1.7976931348623157e308)) {
+        set_error("delta must be finite and >= 0");
+        return CF_INVALID_INPUT_ERROR;
+    }
+    if (delta > 0.0 && (h->nseries != 1 || h->nranks != 1)) {
+        set_error("delta > 0 is supported for a single series on one GPU");
+        return CF_INVALID_INPUT_ERROR;
+    }
+    if (delta != h->delta) h->win_f = -1.0;
+    h->delta = delta;
+    return CF_OK;
+}
+
+double cf_lowess_delta(const cf_lowess* h) { return h ? h->delta : 0.0; }
+
+int32_t cf_lowess_fitted(cf_lowess* h, int32_t* count, int32_t* idx, int32_t cap)
+{
+    if (!h || !h->init) { set_error("No data has been defined."); return CF_NO_DATA_DEFINED_ERROR; }
+    if (!(h->delta > 0.0) || h->delta_built != h->delta) {
+        set_error("no fitted-point list: delta = 0 or no pass has run with this delta");
+        return CF_INVALID_INPUT_ERROR;
+    }
+    CF_TRY(use_device(h));
+    if (count) *count = h->nfit;
+    if (idx && cap > 0) {
+        const int32_t m = h->nfit < cap ? h->nfit : cap;
+        CF_CUDA(cudaMemcpyAsync(idx, h->fidx, sizeof(int32_t) * (size_t)m, cudaMemcpyDeviceToHost, h->stream));
+        CF_CUDA(cudaStreamSynchronize(h->stream));
+        for (int32_t k = 0; k < m; ++k) idx[k] += 1;    // 1-based like every index of this ABI
+    }
+    return CF_OK;
+}
 
 int32_t cf_lowess_reset_windows(cf_lowess* h)
 {
@@ -603,6 +644,7 @@ static void pool_release(cf_lowess* h, int rc)
         std::lock_guard<std::mutex> lk(g_pool_mu);
         if (g_pool.size() < 8) {
             h->rank = 0; h->nranks = 1;
+            h->delta = 0.0;
             g_pool.push_back(h);
             return;
         }
@@ -659,6 +701,27 @@ int32_t cf_lowess_smooth(const double* x_sorted, const double* y, int32_t n, dou
     if (rc == CF_OK) rc = cf_lowess_run(h, f, nsteps, nullptr);
     if (rc == CF_OK) {
         if (n < 2) rc = cf_lowess_fetch(h, ys, nullptr, nullptr);     // rw, res untouched (:651-654)
+        else rc = cf_lowess_fetch(h, ys, nsteps > 0 ? rw : nullptr, res);
+    }
+    pool_release(h, rc);
+    return rc;
+}
+
+int32_t cf_lowess_smooth_delta(const double* x_sorted, const double* y, int32_t n, double f,
+                               int32_t nsteps, double delta, double* ys, double* rw, double* res)
+{
+    if (n < 0 || (n > 0 && (!x_sorted || !y || !ys))) {
+        set_error("Input array sizes must match.");
+        return CF_ARRAY_SIZE_ERROR;
+    }
+    if (nsteps < 0) { set_error("nsteps must be >= 0"); return CF_INVALID_INPUT_ERROR; }
+    cf_lowess* h = nullptr;
+    CF_TRY(pool_acquire(&h));
+    int rc = cf_lowess_set_delta(h, delta);
+    if (rc == CF_OK) rc = cf_lowess_init(h, x_sorted, y, n, 0);
+    if (rc == CF_OK) rc = cf_lowess_run(h, f, nsteps, nullptr);
+    if (rc == CF_OK) {
+        if (n < 2) rc = cf_lowess_fetch(h, ys, nullptr, nullptr);
         else rc = cf_lowess_fetch(h, ys, nsteps > 0 ? rw : nullptr, res);
     }
     pool_release(h, rc);

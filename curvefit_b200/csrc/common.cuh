@@ -135,6 +135,16 @@ struct cf_lowess {
     size_t tree_bytes = 0;
     int method = 0;            // CF_METHOD_DIRECT / CF_METHOD_TREE / CF_METHOD_AUTO
 
+    // delta > 0 (delta.cu): lowest() runs only at the fitted points fidx[0..nfit), the
+    // rest is tie-copied / interpolated (src/curvefit_regression.f90:674-690)
+    double delta = 0.0;
+    double delta_built = -1.0;           // delta the lists below were built for
+    int32_t nfit = 0;
+    int32_t* fidx = nullptr;             // fitted points, ascending
+    int32_t* fcend = nullptr;            // end of the tie chain of each fitted point (`last`, :681-689)
+    int32_t* frank = nullptr;            // n + 1: number of fitted points < p
+    int64_t cap_delta = 0;
+
     // peer-memory exchange (peer.cu); comm is this rank's own block
     cf::PeerComm* comm = nullptr;
     cf::PeerPtrs peer = {};
@@ -153,6 +163,9 @@ int launch_fit(cf_lowess* h, bool use_rw);        // dispatches on h->method
 int launch_fit_tree(cf_lowess* h, bool use_rw);   // tree.cu
 bool method_is_tree(const cf_lowess* h);
 int launch_residuals(cf_lowess* h);           // tie copy + res = y - ys on the shard
+int delta_prepare(cf_lowess* h);              // delta.cu: (re)build the fitted-point list
+int launch_delta_fill(cf_lowess* h);          // delta.cu: tie copy + interpolation + res
+void delta_free(cf_lowess* h);
 int launch_select_reset(cf_lowess* h);
 int launch_hist(cf_lowess* h, int round);
 int launch_pick(cf_lowess* h, int round);

@@ -41,7 +41,14 @@ struct FitParams {
     Windows w;
     int32_t n, ns, begin, end, ksplit;
     int32_t tiles;      // tiles per series
+    const int32_t* fidx;  // delta > 0: output slot -> point (delta.cu); then begin = 0, end = #fitted
 };
+
+// output slot -> index of the point fitted there
+__device__ __forceinline__ int32_t slot_point(const FitParams& prm, int32_t slot)
+{
+    return prm.fidx ? __ldg(prm.fidx + slot) : slot;
+}
 
 // batched mode: series blockIdx.y occupies [series * n, (series + 1) * n) of every array
 __device__ __forceinline__ FitParams for_series(const FitParams& in, int series)
@@ -119,11 +126,12 @@ __device__ __forceinline__ void tile_setup(const FitParams& prm, int32_t tile0, 
 #pragma unroll
     for (int p = 0; p < P; ++p) {
         const int loc = wid * (32 * P) + p * 32 + lane;
-        const int32_t i = tile0 + loc;
         // tie followers copy their leader's value later (robust.cu); a shard that
-        // starts inside a tie group fits its first point in the leader's place
-        bool v = i < tile_end;
-        if (v) {
+        // starts inside a tie group fits its first point in the leader's place.
+        // With a fitted-point list every slot is fitted.
+        bool v = tile0 + loc < tile_end;
+        const int32_t i = v ? slot_point(prm, tile0 + loc) : 0;
+        if (v && !prm.fidx) {
             const int32_t l = prm.w.leader[i];
             v = (l == i) || (i == prm.begin && l < i);
         }
@@ -173,7 +181,7 @@ __device__ __forceinline__ void tile_setup(const FitParams& prm, int32_t tile0, 
     if (!(hc > 0.0)) hc = 1.0;
     t.hc = hc;
     t.sc = 1.0 / hc;
-    t.xc = x[min(tile0 + T / 2, prm.n - 1)];
+    t.xc = x[slot_point(prm, min(tile0 + T / 2, (prm.fidx ? prm.end : prm.n) - 1))];
 }
 
 template <int NT, int P, int E>
@@ -381,7 +389,7 @@ fit_kernel(const FitParams prm_in)
 #pragma unroll
     for (int p = 0; p < P; ++p) {
         if (!t.valid[p]) continue;
-        const int32_t i = tile0 + wid * (32 * P) + p * 32 + lane;
+        const int32_t i = slot_point(prm, tile0 + wid * (32 * P) + p * 32 + lane);
         const double scale = exact ? t.hp[p] : t.hc;
         const double us = exact ? 0.0 : (t.xsp[p] - xc) * sc;
         prm.ys[i] = fit_value(S0[p], S1[p], S2[p], T0[p], T1[p], y[i], t.hp[p], scale, us, range);
@@ -418,7 +426,7 @@ fit_finalize_kernel(const FitParams prm_in)
 #pragma unroll
             for (int q = 0; q < 5; ++q) m[q] += src[((size_t)k * 5 + q) * T + loc];
         }
-        const int32_t i = tile0 + loc;
+        const int32_t i = slot_point(prm, tile0 + loc);
         const double scale = t.exact ? t.hp[p] : t.hc;
         const double us = t.exact ? 0.0 : (t.xsp[p] - t.xc) * t.sc;
         prm.ys[i] = fit_value(m[0], m[1], m[2], m[3], m[4], prm.y[i], t.hp[p], scale, us, range);
@@ -439,7 +447,7 @@ int launch_variant(cf_lowess* h, FitParams& prm, int sms)
         CF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_set = true;
     }
-    const int tiles = (h->end - h->begin + T - 1) / T;
+    const int tiles = (prm.end - prm.begin + T - 1) / T;
     const long long all_tiles = (long long)tiles * h->nseries;
     prm.tiles = tiles;
     // K-way split of every tile's window when the tiles alone give too few waves
@@ -497,7 +505,8 @@ int launch_fit(cf_lowess* h, bool use_rw)
     FitParams prm;
     prm.x = h->x; prm.y = h->y; prm.rw = use_rw ? h->rw : nullptr; prm.ys = h->ys;
     prm.w = h->win; prm.n = h->n; prm.ns = h->ns; prm.begin = h->begin; prm.end = h->end;
-    prm.ksplit = 1; prm.part = nullptr;
+    prm.ksplit = 1; prm.part = nullptr; prm.fidx = nullptr;
+    if (h->delta > 0.0) { prm.fidx = h->fidx; prm.begin = 0; prm.end = h->nfit; }
     if (h->sms <= 0) {
         int sms = 0;
         CF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));

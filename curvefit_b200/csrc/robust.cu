@@ -33,6 +33,7 @@ residual_kernel(const double* __restrict__ y, double* __restrict__ ys,
 
 int launch_residuals(cf_lowess* h)
 {
+    if (h->delta > 0.0) return launch_delta_fill(h);   // interpolation + tie copy + residuals
     const int cnt = h->end - h->begin;
     if (cnt <= 0) return CF_OK;
     residual_kernel<<<dim3((cnt + 255) / 256, h->nseries), 256, 0, h->stream>>>(

@@ -46,6 +46,7 @@ struct TreeParams {
     double* ys;
     double* nodes;              // [series][total_nodes][kNodeLen]
     const int32_t* span;        // [series]{min lo9, max hi9} over the shard's points (windows.cu)
+    const int32_t* fidx;        // delta > 0: output slot -> point (delta.cu); begin = 0, end = #fitted
     Windows w;
     int32_t n, ns, begin, end;
     int32_t nlevels;
@@ -341,12 +342,13 @@ tree_eval_kernel(const TreeParams prm)
     const double* __restrict__ y = prm.y + soff;
     const double* __restrict__ rw = prm.rw ? prm.rw + soff : nullptr;
     const double* __restrict__ nodes = prm.nodes + (size_t)blockIdx.y * prm.total * kNodeLen;
-    const int32_t i = prm.begin + blockIdx.x * NT + threadIdx.x;
+    const int32_t slot = prm.begin + blockIdx.x * NT + threadIdx.x;
 
     // tie followers copy their leader's value later (robust.cu); a shard that starts
     // inside a tie group fits its first point in the leader's place (as fit.cu)
-    bool valid = i < prm.end;
-    if (valid) {
+    bool valid = slot < prm.end;
+    const int32_t i = (valid && prm.fidx) ? __ldg(prm.fidx + slot) : slot;
+    if (valid && !prm.fidx) {
         const int32_t l = prm.w.leader[soff + i];
         valid = (l == i) || (i == prm.begin && l < i);
     }
@@ -460,6 +462,8 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
     TreeParams prm = {};
     prm.x = h->x; prm.y = h->y; prm.rw = use_rw ? h->rw : nullptr; prm.ys = h->ys;
     prm.w = h->win; prm.n = h->n; prm.ns = h->ns; prm.begin = h->begin; prm.end = h->end;
+    prm.fidx = nullptr;
+    if (h->delta > 0.0) { prm.fidx = h->fidx; prm.begin = 0; prm.end = h->nfit; }
     int L = 0;
     int64_t total = 0;
     int32_t cnt = (h->n + kLeaf - 1) / kLeaf;
@@ -499,7 +503,7 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
         h->launches++;
     }
     constexpr int NT = 128;
-    const int cntp = h->end - h->begin;
+    const int cntp = prm.end - prm.begin;
     tree_eval_kernel<NT><<<dim3((cntp + NT - 1) / NT, h->nseries), NT, 0, h->stream>>>(prm);
     CF_CUDA(cudaGetLastError());
     h->launches++;

@@ -17,14 +17,15 @@ __device__ __forceinline__ void windows_point(const double* __restrict__ x, int3
 
 __global__ void __launch_bounds__(256)
 windows_kernel(const double* __restrict__ x, int32_t n, int32_t ns, Windows w, int32_t begin,
-               int32_t end, int32_t* __restrict__ span)
+               int32_t end, int32_t* __restrict__ span, const int32_t* __restrict__ fidx)
 {
     // only the handle's shard [begin, end) of output points is searched; span[0..1]
-    // receives min lo9 / max hi9 over it (the elements its fits can touch)
-    const int32_t i0 = begin + blockIdx.x * blockDim.x + threadIdx.x;
-    const bool live = i0 < end;
+    // receives min lo9 / max hi9 over it (the elements its fits can touch).  delta > 0
+    // (delta.cu): slots [begin, end) of the fitted-point list fidx instead.
+    const int32_t s0 = begin + blockIdx.x * blockDim.x + threadIdx.x;
+    const bool live = s0 < end;
     int32_t l9 = INT32_MAX, r9 = -1;
-    if (live) windows_point(x, n, ns, w, i0, l9, r9);
+    if (live) windows_point(x, n, ns, w, fidx ? fidx[s0] : s0, l9, r9);
     l9 = __reduce_min_sync(0xffffffffu, l9);
     r9 = __reduce_max_sync(0xffffffffu, r9);
     if ((threadIdx.x & 31) == 0 && r9 >= 0) {
@@ -123,12 +124,14 @@ int launch_windows(cf_lowess* h, int32_t ns)
 {
     if (h->n < 2) return CF_OK;
     const int threads = 256;
-    const int cnt = h->end - h->begin;
+    const bool listed = h->delta > 0.0;
+    const int32_t begin = listed ? 0 : h->begin, end = listed ? h->nfit : h->end;
+    const int cnt = end - begin;
     span_init_kernel<<<(h->nseries + 255) / 256, 256, 0, h->stream>>>(h->span, h->nseries);
     if (cnt <= 0) return CF_OK;
     const int blocks = (cnt + threads - 1) / threads;
-    windows_kernel<<<dim3(blocks, h->nseries), threads, 0, h->stream>>>(h->x, h->n, ns, h->win, h->begin,
-                                                                        h->end, h->span);
+    windows_kernel<<<dim3(blocks, h->nseries), threads, 0, h->stream>>>(h->x, h->n, ns, h->win, begin, end,
+                                                                        h->span, listed ? h->fidx : nullptr);
     CF_CUDA(cudaGetLastError());
     h->launches++;
     return CF_OK;

@@ -92,6 +92,29 @@ class lowess_smoothing:
         if rc != 0:
             raise RuntimeError(f"cf_lowess_set_method failed ({rc}): {_lib.last_error()}")
 
+    def set_delta(self, delta: float) -> None:
+        """m_delta (:230): lowess's interpolation distance.  The reference fixes it at 0
+        (:807; the setter is a stub, :808-809); delta > 0 fits only points more than delta
+        apart and interpolates the rest (:674-690).  Extension; see curvefit_cuda.h."""
+        rc = self._handle()
+        if rc == 0:
+            rc = self._lib.cf_lowess_set_delta(self._h, float(delta))
+        if rc != 0:
+            raise RuntimeError(f"cf_lowess_set_delta failed ({rc}): {_lib.last_error()}")
+        self.m_delta = float(delta)
+
+    def fitted_points(self) -> np.ndarray:
+        """1-based indices of the points lowest() ran at in the last delta > 0 smooth."""
+        cnt = C.c_int32(0)
+        rc = self._lib.cf_lowess_fitted(self._h, C.byref(cnt), None, 0)
+        if rc != 0:
+            raise RuntimeError(f"cf_lowess_fitted failed ({rc}): {_lib.last_error()}")
+        idx = np.zeros(cnt.value, np.int32)
+        rc = self._lib.cf_lowess_fitted(self._h, C.byref(cnt), _ip(idx), idx.size)
+        if rc != 0:
+            raise RuntimeError(f"cf_lowess_fitted failed ({rc}): {_lib.last_error()}")
+        return idx
+
     # -- ls_init (:740-811) ---------------------------------------------------------
     def initialize(self, x, y, srt: bool = True, err: Optional[errors] = None) -> None:
         self.m_init = False                                   # :758
@@ -118,7 +141,9 @@ class lowess_smoothing:
         # allocated but not initialised in the reference (:780-784)
         self.m_weights = np.zeros(n)
         self.m_residuals = np.zeros(n)
-        self.m_delta = 0.0                                    # :807
+        if self.m_delta != 0.0:                               # :807 -- initialize resets delta
+            self._lib.cf_lowess_set_delta(self._h, 0.0)
+        self.m_delta = 0.0
         self.m_init = True                                    # :810
 
     # -- ls_smooth (:832-868) -----------------------------------------------------
@@ -287,6 +312,20 @@ def cf_lowess_smooth(x_sorted, y, f, nsteps=2, out=None):
     rc = lib.cf_lowess_smooth(_dp(x), _dp(y), n, float(f), int(nsteps), _dp(ys), _dp(rw), _dp(res))
     if rc != 0:
         raise RuntimeError(f"cf_lowess_smooth failed ({rc}): {_lib.last_error()}")
+    return ys, rw, res
+
+
+def cf_lowess_smooth_delta(x_sorted, y, f, nsteps=2, delta=0.0):
+    """lowess(x, y, f, nsteps, delta, ys, rw, res) (:625-715) through the host-buffer C ABI."""
+    lib = _lib.load()
+    x = np.ascontiguousarray(x_sorted, dtype=np.float64)
+    y = np.ascontiguousarray(y, dtype=np.float64)
+    n = x.size
+    ys, rw, res = np.empty(n), np.zeros(n), np.zeros(n)
+    rc = lib.cf_lowess_smooth_delta(_dp(x), _dp(y), n, float(f), int(nsteps), float(delta),
+                                    _dp(ys), _dp(rw), _dp(res))
+    if rc != 0:
+        raise RuntimeError(f"cf_lowess_smooth_delta failed ({rc}): {_lib.last_error()}")
     return ys, rw, res
 
 

@@ -77,6 +77,15 @@ CF_API int32_t cf_lowess_smooth(const double* x_sorted, const double* y, int32_t
                                 double f, int32_t nsteps,
                                 double* ys, double* rw, double* res);
 
+/* The same with delta > 0 -- lowess's interpolation mode (:674-690): lowest() runs
+ * only at points more than delta apart, points in between are linearly interpolated
+ * (:675-679), points closer than epsilon to the last fitted one copy it (:685-688).
+ * The reference's smooth() always passes delta = 0 (:807, :866), so this is an
+ * extension of the drop-in surface; results equal the reference's lowess(delta). */
+CF_API int32_t cf_lowess_smooth_delta(const double* x_sorted, const double* y, int32_t n,
+                                      double f, int32_t nsteps, double delta,
+                                      double* ys, double* rw, double* res);
+
 /* nseries independent series, row-major [nseries][n]; same semantics per row. */
 CF_API int32_t cf_lowess_smooth_batched(const double* x_sorted, const double* y,
                                         int32_t nseries, int32_t n, double f,
@@ -143,6 +152,14 @@ CF_API int32_t cf_lowess_shard(const cf_lowess* h, int32_t* begin, int32_t* end,
 #define CF_METHOD_AUTO 2
 CF_API int32_t cf_lowess_set_method(cf_lowess* h, int32_t method);
 CF_API int32_t cf_lowess_method(const cf_lowess* h);
+
+/* delta of later runs on this handle (default 0 = every distinct x is fitted).
+ * delta > 0: single series, one GPU (no batched / sharded handles). */
+CF_API int32_t cf_lowess_set_delta(cf_lowess* h, double delta);
+CF_API double cf_lowess_delta(const cf_lowess* h);
+/* After a run with delta > 0: number of points lowest() was called on and their
+ * 1-based indices (first min(count, cap) of them; idx may be NULL). */
+CF_API int32_t cf_lowess_fitted(cf_lowess* h, int32_t* count, int32_t* idx, int32_t cap);
 
 /* The neighbourhoods (windows.cu) depend only on x and f, so a handle keeps them
  * between runs with the same f.  This drops them: the next run recomputes them,
