@@ -9,10 +9,11 @@ library or without a CUDA device every operation raises.
 from .core import (CF_ARRAY_SIZE_ERROR, CF_DEVICE_ERROR, CF_INVALID_INPUT_ERROR,
                    CF_NO_DATA_DEFINED_ERROR, CF_OUT_OF_MEMORY_ERROR, CurvefitError)
 from .errors import errors
-from .regression import lowess_smoothing
+from .regression import lowess_smoothing, moving_average
+from .statistics import median
 
 __all__ = [
-    "lowess_smoothing", "errors", "CurvefitError",
+    "lowess_smoothing", "moving_average", "median", "errors", "CurvefitError",
     "CF_ARRAY_SIZE_ERROR", "CF_OUT_OF_MEMORY_ERROR", "CF_NO_DATA_DEFINED_ERROR",
     "CF_INVALID_INPUT_ERROR", "CF_DEVICE_ERROR",
 ]

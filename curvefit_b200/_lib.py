@@ -44,6 +44,11 @@ SIGNATURES = {
     "cf_lowess_fitted": (C.c_int32, [C.c_void_p, c_ip, c_ip, C.c_int32]),
     "cf_lowess_smooth_batched": (C.c_int32, [c_dp, c_dp, C.c_int32, C.c_int32, C.c_double, C.c_int32,
                                              c_dp, c_dp, c_dp]),
+    "cf_moving_average": (C.c_int32, [c_dp, C.c_int32, C.c_int32]),
+    "cf_moving_average_device": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
+    "cf_median": (C.c_int32, [c_dp, C.c_int32, c_dp]),
+    "cf_median_device": (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),
+    "cf_sort": (C.c_int32, [c_dp, C.c_int32, c_dp]),
     "cf_lowess_create": (C.c_int32, [C.POINTER(C.c_void_p), C.c_int32, C.c_void_p]),
     "cf_lowess_destroy": (None, [C.c_void_p]),
     "cf_lowess_init": (C.c_int32, [C.c_void_p, c_dp, c_dp, C.c_int32, C.c_int32]),

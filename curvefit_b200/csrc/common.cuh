@@ -45,6 +45,19 @@ struct SelectState {
 };
 
 #ifdef __CUDACC__
+// order-preserving uint64 image of a double (negative values: all bits flipped;
+// non-negative: sign bit set) and its inverse
+__device__ __forceinline__ unsigned long long ordered_key(double v)
+{
+    const unsigned long long b = (unsigned long long)__double_as_longlong(v);
+    return (b >> 63) ? ~b : (b | 0x8000000000000000ull);
+}
+__device__ __forceinline__ double ordered_value(unsigned long long k)
+{
+    const unsigned long long b = (k >> 63) ? (k & 0x7fffffffffffffffull) : ~k;
+    return __longlong_as_double((long long)b);
+}
+
 // local linear fit evaluated at xs from the five moments (:559-584)
 __device__ __forceinline__ double fit_value(double S0, double S1, double S2, double T0, double T1,
                                             double yi, double h, double scale, double us,
@@ -170,6 +183,7 @@ int launch_select_reset(cf_lowess* h);
 int launch_hist(cf_lowess* h, int round);
 int launch_pick(cf_lowess* h, int round);
 int launch_bisquare(cf_lowess* h);
+int select_median(cf_lowess* h, const double* d_x, int32_t n, double* d_out);   // robust.cu
 int launch_peer_barrier(cf_lowess* h);        // peer.cu: all ranks reach this point
 int launch_peer_gather(cf_lowess* h, int what);  // peer.cu: own ys/res/rw block -> every rank
 int launch_peer_spans(cf_lowess* h);          // peer.cu: publish the shard's element span, learn the peers'

@@ -79,7 +79,7 @@ int launch_select_reset(cf_lowess* h)
 
 __global__ void __launch_bounds__(512)
 hist_kernel(const double* __restrict__ res, int32_t begin, int32_t end, int32_t n, int round,
-            const SelectState* __restrict__ st, unsigned long long* __restrict__ hist)
+            const SelectState* __restrict__ st, unsigned long long* __restrict__ hist, int ordered)
 {
     __shared__ unsigned int sh[kHistLen];
     res += (size_t)blockIdx.y * (size_t)n;
@@ -93,8 +93,9 @@ hist_kernel(const double* __restrict__ res, int32_t begin, int32_t end, int32_t 
     const int hs = shift + width;  // bits below the resolved prefix
     const int32_t stride = gridDim.x * blockDim.x;
     for (int32_t i = begin + blockIdx.x * blockDim.x + threadIdx.x; i < end; i += stride) {
-        const unsigned long long key =
-            (unsigned long long)__double_as_longlong(fabs(res[i]));           // :697
+        // ordered = 0: |res| (:697); 1: order-preserving image of the signed value (stats.cu)
+        const unsigned long long key = ordered ? ordered_key(res[i])
+            : (unsigned long long)__double_as_longlong(fabs(res[i]));
         const unsigned long long hi = hs >= 64 ? 0ull : (key >> hs);
         const unsigned d = (unsigned)(key >> shift) & mask;
         if (hi == p0) atomicAdd(&sh[d], 1u);
@@ -112,11 +113,12 @@ int launch_hist(cf_lowess* h, int round)
     int blocks = (cnt + 512 * 8 - 1) / (512 * 8);
     if (blocks > 148 * 4) blocks = 148 * 4;
     hist_kernel<<<dim3(blocks, h->nseries), 512, 0, h->stream>>>(h->res, h->begin, h->end, h->n,
-                                                                 round, h->sel, h->hist);
+                                                                 round, h->sel, h->hist, 0);
     CF_CUDA(cudaGetLastError());
     h->launches++;
     return CF_OK;
 }
+
 
 // One warp per tracked rank: locate the bin holding the rank, extend the prefix,
 // rebase the rank, clear the histogram for the next round; after the last round
@@ -236,6 +238,30 @@ int launch_bisquare(cf_lowess* h)
         h->res, h->rw, h->sel, h->begin, h->end, h->n, PeerPtrs{});
     CF_CUDA(cudaGetLastError());
     h->launches++;
+    return CF_OK;
+}
+
+// The two middle order statistics of an arbitrary device array (median_dbl,
+// src/curvefit_statistics.f90:273-292), with the handle's select state as scratch:
+// out = x(nmidp1) for odd n, half * (x(nmid) + x(nmidp1)) for even n.
+__global__ void median_finish_kernel(const SelectState* st, int32_t n, double* out)
+{
+    const double lo = ordered_value(st->prefix[0]), hi = ordered_value(st->prefix[1]);
+    *out = (n & 1) ? hi : __dmul_rn(0.5, __dadd_rn(lo, hi));
+}
+
+int select_median(cf_lowess* h, const double* d_x, int32_t n, double* d_out)
+{
+    select_reset_kernel<<<1, 256, 0, h->stream>>>(h->sel, h->hist, n);
+    int blocks = (n + 512 * 8 - 1) / (512 * 8);
+    if (blocks > 148 * 4) blocks = 148 * 4;
+    for (int r = 0; r < kSelRounds; ++r) {
+        hist_kernel<<<blocks, 512, 0, h->stream>>>(d_x, 0, n, n, r, h->sel, h->hist, 1);
+        pick_kernel<false><<<1, 64, 0, h->stream>>>(h->sel, h->hist, r, PeerPtrs{}, 0ull);
+    }
+    median_finish_kernel<<<1, 1, 0, h->stream>>>(h->sel, n, d_out);
+    CF_CUDA(cudaGetLastError());
+    h->launches += 2 + 2 * kSelRounds;
     return CF_OK;
 }
 

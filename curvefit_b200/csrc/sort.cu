@@ -179,7 +179,7 @@ __global__ void sort_finish_kernel(const unsigned long long* __restrict__ keys,
     if (i >= n) return;
     const uint32_t s = idx[i];
     x_out[i] = val_of(keys[i]);
-    y_out[i] = y_in[s];                          // m_y = y(indices), :798
+    if (y_out) y_out[i] = y_in[s];               // m_y = y(indices), :798
     if (perm) perm[i] = (int32_t)s + 1;          // 1-based like the tracking array
 }
 

@@ -17,8 +17,8 @@ from typing import Optional
 import numpy as np
 
 from . import _lib
-from .core import (CF_ARRAY_SIZE_ERROR, CF_DEVICE_ERROR, CF_NO_DATA_DEFINED_ERROR,
-                   CF_OUT_OF_MEMORY_ERROR)
+from .core import (CF_ARRAY_SIZE_ERROR, CF_DEVICE_ERROR, CF_INVALID_INPUT_ERROR,
+                   CF_NO_DATA_DEFINED_ERROR, CF_OUT_OF_MEMORY_ERROR)
 from .errors import errors
 
 _MESSAGES = {
@@ -37,6 +37,25 @@ def _dp(a: Optional[np.ndarray]):
 
 def _ip(a: Optional[np.ndarray]):
     return None if a is None else a.ctypes.data_as(_lib.c_ip)
+
+
+def moving_average(x: np.ndarray, npts: int, err: Optional[errors] = None) -> None:
+    """moving_average_1 (src/curvefit_regression.f90:427-478): smooths the signal x IN
+    PLACE with an npts-sample moving average (zeros before the start of the signal,
+    running-update mean).  x must be a contiguous float64 array.  Errors as the reference:
+    npts < 2 or npts > size(x) -> CF_INVALID_INPUT_ERROR through `err`, x untouched."""
+    errmgr = err if err is not None else errors()             # :443-448
+    if not (isinstance(x, np.ndarray) and x.dtype == np.float64 and x.flags.c_contiguous and x.ndim == 1):
+        raise TypeError("x must be a contiguous 1-d float64 array (it is smoothed in place)")
+    n = x.size
+    if npts < 2 or npts > n:                                  # :452-457
+        errmgr.report_error("moving_average_1", "The averaging size window must be at least 2, and less "
+                            "than the size of the data set.", CF_INVALID_INPUT_ERROR)
+        return
+    rc = _lib.load().cf_moving_average(_dp(x), n, int(npts))
+    if rc != 0:
+        msg = _MESSAGES.get(rc) or _lib.last_error() or "CUDA device failure."
+        errmgr.report_error("moving_average_1", msg, rc)
 
 
 class lowess_smoothing:

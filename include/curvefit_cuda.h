@@ -93,6 +93,32 @@ CF_API int32_t cf_lowess_smooth_batched(const double* x_sorted, const double* y,
                                         double* ys, double* rw, double* res);
 
 /* ------------------------------------------------------------------------
+ * Neighbours of the LOWESS path (stats.cu).
+ * ---------------------------------------------------------------------- */
+
+/* moving_average_1(x, npts) (src/curvefit_regression.f90:427-478), in place on a
+ * HOST array: x(i) <- mean of the last npts samples, zeros before the start of
+ * the signal (:467-473), mean by the running update of mean_dbl
+ * (src/curvefit_statistics.f90:239-242).  Bit-identical to the reference.
+ * npts < 2 or npts > n: CF_INVALID_INPUT_ERROR (:452-457), x untouched. */
+CF_API int32_t cf_moving_average(double* x, int32_t n, int32_t npts);
+/* Same on device memory, out of place, asynchronous on `stream` (a cudaStream_t). */
+CF_API int32_t cf_moving_average_device(const void* d_x, void* d_out, int32_t n,
+                                        int32_t npts, void* stream);
+
+/* median_dbl (src/curvefit_statistics.f90:258-295) of a host array: an exact radix
+ * select of the two middle order statistics instead of the reference's full sort
+ * (:286); *z = x(nmidp1) for odd n, half * (x(nmid) + x(nmidp1)) for even n, 0 for
+ * n = 0 (:280-283).  x is not modified; a caller that wants the reference's
+ * srt = .true. side effect (x sorted on return) calls cf_sort as well. */
+CF_API int32_t cf_median(const double* x, int32_t n, double* z);
+CF_API int32_t cf_median_device(const void* d_x, int32_t n, void* d_z, void* stream);
+
+/* sort(x, .true.) (LINALG linalg_sorting.f90:12-35 -> DLASRT 'I'): ascending values
+ * by the device radix sort.  In and out may not alias. */
+CF_API int32_t cf_sort(const double* x, int32_t n, double* x_sorted);
+
+/* ------------------------------------------------------------------------
  * Device-resident handle -- the lowess_smoothing object's state on one GPU
  * (m_x, m_y, m_weights, m_residuals: src/curvefit_regression.f90:218-233).
  * ---------------------------------------------------------------------- */

@@ -22,8 +22,8 @@ _ip = C.POINTER(C.c_int)
 
 def build(force: bool = False) -> str:
     """Compile the C restatement with oracle/Makefile (gcc, no FMA contraction)."""
-    src = os.path.join(_HERE, "lowess_oracle.c")
-    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+    srcs = [os.path.join(_HERE, f) for f in ("lowess_oracle.c", "stats_oracle.c")]
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < max(os.path.getmtime(f) for f in srcs):
         env = dict(os.environ)
         env.pop("CC", None)
         subprocess.run(["make", "-C", _HERE, "-B"], check=True, env=env,
@@ -60,6 +60,10 @@ def lib() -> C.CDLL:
         L.cf_oracle_ls_init.restype = C.c_int
         L.cf_oracle_ls_smooth.argtypes = [_dp, _dp, C.c_int, C.c_double, _dp, _dp, _dp]
         L.cf_oracle_ls_smooth.restype = C.c_int
+        L.cf_oracle_moving_average.argtypes = [_dp, C.c_int, C.c_int]
+        L.cf_oracle_moving_average.restype = C.c_int
+        L.cf_oracle_median.argtypes = [_dp, C.c_int, C.c_int]
+        L.cf_oracle_median.restype = C.c_double
         L.cf_oracle_max_threads.argtypes = []
         L.cf_oracle_max_threads.restype = C.c_int
         _lib = L
@@ -162,3 +166,18 @@ def ls_init(x, y, srt=True):
 
 def max_threads() -> int:
     return int(lib().cf_oracle_max_threads())
+
+
+def moving_average(x, npts):
+    """moving_average_1 (src/curvefit_regression.f90:427-478) on a copy; returns
+    (smoothed, flag) with flag = 0 or the reference's error code."""
+    out = _f64(x).copy()
+    rc = lib().cf_oracle_moving_average(_d(out), out.size, int(npts))
+    return out, rc
+
+
+def median(x, srt=True):
+    """median_dbl (src/curvefit_statistics.f90:258-295); returns (z, x after the call)."""
+    a = _f64(x).copy()
+    z = lib().cf_oracle_median(_d(a), a.size, 1 if srt else 0)
+    return float(z), a

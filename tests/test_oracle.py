@@ -179,3 +179,34 @@ def test_oracle_reproduces_golden_vectors(oracle, name):
         r = oracle.lowess(g["x"], g["y"], float(g["f"]), int(g["nsteps"]), want_windows=True)
         for k in ("ys", "rw", "res", "cmad", "nleft", "nright", "nrt"):
             assert np.array_equal(r[k], g[k]), k
+
+
+# ---- neighbours of the path: moving_average, median (oracle/stats_oracle.c) ----------------
+def test_median_oracle_known_answer(oracle):
+    """The reference's own known-answer test, tests/curvefit_test_statistics.f90:286-309."""
+    z, xs = oracle.median([2.0, 3.0, 1.0, -4.0, -7.0, 1.0, 3.0])
+    assert z == 1.0
+    assert list(xs) == [-7.0, -4.0, 1.0, 1.0, 2.0, 3.0, 3.0]
+    assert oracle.median([])[0] == 0.0
+    assert oracle.median([4.0, 1.0])[0] == 2.5
+    assert oracle.median([1.0, 4.0, 9.0], srt=False)[0] == 4.0
+
+
+def test_moving_average_oracle_against_python_transliteration(oracle):
+    """Independent restatement of src/curvefit_regression.f90:467-477 with mean_dbl
+    (src/curvefit_statistics.f90:239-242) in plain Python floats (IEEE double)."""
+    rng = np.random.default_rng(8)
+    for n, npts in [(2, 2), (12, 3), (50, 50), (200, 17)]:
+        x = rng.normal(size=n)
+        buf = [0.0] * npts
+        want = []
+        for v in x:
+            buf = [float(v)] + buf[:-1]
+            z = buf[0]
+            for k in range(2, npts + 1):
+                z = z + (buf[k - 1] - z) / k
+            want.append(z)
+        got, rc = oracle.moving_average(x, npts)
+        assert rc == 0 and np.array_equal(got, np.array(want))
+    assert oracle.moving_average(np.zeros(5), 1)[1] == 201
+    assert oracle.moving_average(np.zeros(5), 6)[1] == 201
