@@ -213,6 +213,8 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     n, f, nsteps, wname = WORKLOADS[args.workload]
     x, y = make_data(n)
+    if args.method != "direct":
+        os.environ["CF_LOWESS_METHOD"] = args.method     # the stateless e2e calls use it too
     lib = _lib.load()
     ns = lib.cf_lowess_span(n, f)
 
@@ -286,7 +288,15 @@ def run_ours(args):
             "gpu_launches": launches,
             "clocks": clk.summary(),
         }
-        if world == 1 and fit_launches:
+        if world == 1 and fit_launches and args.method != "direct":
+            line["roofline"] = {
+                "bound": "fp64", "achieved": None, "peak": peak_tf, "unit": "TFLOP/s", "frac": None,
+                "traffic": None, "kernel": "cf::tree_eval_kernel",
+                "avg_launch_ms": fit_ms / fit_launches, "share_of_step": fit_ms / total_ms,
+                "note": "moment-tree evaluator: O(n log ns) work, no 17 flop/pair accounting applies; "
+                        "ncu: profiles/r01_tree_eval_c4_ncu_full.csv (FP64 pipe 48% active). The roofline "
+                        "claim of this repo is the direct kernel's (default --method direct)."}
+        elif world == 1 and fit_launches:
             avg_ms = fit_ms / fit_launches
             flops = FLOP_PER_PAIR * n * ns
             ach = flops / (avg_ms * 1e-3) / 1e12
@@ -466,6 +476,8 @@ def run_batched(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     nseries, n, f, nsteps, wname = BATCHED[args.workload]
+    if args.method != "direct":
+        os.environ["CF_LOWESS_METHOD"] = args.method
     mine = nseries // world            # series are independent: partition, no collective
     x, y = make_batched(mine, n, first=rank * mine)
     ns = _lib.load().cf_lowess_span(n, f)
@@ -523,6 +535,10 @@ def run_batched(args):
                          "share_of_step": fit_ms / total_ms,
                          "peak_source": f"measured here: cf_fp64_peak ({peak_mhz:.0f} MHz equiv.)"},
         }
+        line["config"]["method"] = args.method
+        if args.method != "direct":
+            line["roofline"].update({"achieved": None, "frac": None, "kernel": "cf::tree_eval_kernel",
+                                     "note": "moment-tree evaluator: the 17 flop/pair accounting does not apply"})
         if world == 1 and not args.no_e2e:
             k = min(mine, 512)
             xp = torch.from_numpy(x[:k].copy()).pin_memory().numpy()

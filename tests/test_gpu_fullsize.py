@@ -1,0 +1,142 @@
+"""GPU parity at BASELINE.json's FULL sizes (C2, C3, C4, C5), where the oracle cannot run
+a whole smooth() (SURVEY 8c "oracle at sizes it cannot run end-to-end"):
+
+  * teacher forcing -- the oracle's lowest() at stratified sample points (both ends,
+    interior), fed with the robustness weights the GPU itself entered the pass with;
+  * the robustness step in full, O(n) on the host: cmad = 3 * (the two middle order
+    statistics of |res|) by numpy partition, bisquare weights recomputed from (res, cmad)
+    -- both BIT-exact (src/curvefit_regression.f90:697-713 has no summation order);
+  * size-independent properties: exactly linear data is reproduced (ys = y to 1e-10,
+    every robustness weight 1); res == y - ys bitwise.
+Tolerance for values: 1e-10 (tests/cases.close_or_exact)."""
+import numpy as np
+import pytest
+
+from curvefit_b200 import datagen
+from tests import cases
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-10
+
+
+@pytest.fixture(scope="module")
+def cf():
+    from curvefit_b200 import regression
+    return regression
+
+
+def _sample_idx(n, m):
+    return np.unique(np.concatenate([np.arange(0, 3), np.arange(n - 3, n),
+                                     np.linspace(0, n - 1, m).astype(np.int64)])).astype(np.int32)
+
+
+def _bisquare(res, cmad):
+    """:704-713 with the reference's operation order (numpy float64 = IEEE, no FMA)."""
+    r = np.abs(res)
+    c9, c1 = 0.999 * cmad, 0.001 * cmad
+    with np.errstate(divide="ignore", invalid="ignore"):
+        t = r / cmad
+        u = 1.0 - t * t
+        w = u * u
+    w = np.where(r <= c1, 1.0, np.where(r > c9, 0.0, w))
+    return w
+
+
+def _check_robust_step(fit, f, y):
+    """One more pass from the GPU's own weights, then the robustness step on its residuals,
+    verified in full on the host."""
+    n = y.size
+    rw_in = fit.m_weights.copy()
+    ys1, rw1, res1 = fit.run_from_rw(f, rw_in, passes=2)      # pass, robust update, pass
+    ys0, _, res0 = fit.run_from_rw(f, rw_in, passes=1)        # the first of the two passes again
+    assert np.array_equal(res0, y - ys0)                      # :695, bitwise
+    a = np.abs(res0)
+    m1, m2 = n // 2, n - (1 + n // 2)                         # 0-based ranks of rw(m1), rw(m2), :699-700
+    part = np.partition(a, [m2, m1])
+    cmad = 3.0 * (part[m1] + part[m2])                        # :701
+    assert np.array_equal(rw1, _bisquare(res0, cmad))         # select + bisquare: bit-exact
+    return rw_in, ys0
+
+
+def _teacher(cf_fit, oracle, x, y, f, rw_in, ys_pass, m):
+    idx = _sample_idx(x.size, m)
+    t = oracle.lowest_at(x, y, f, idx, rw_in)
+    ok, d, nref = cases.close_or_exact(ys_pass[idx], t["ys"], x, y, rw_in, f, TOL, idx=idx)
+    assert ok, (d, nref)
+
+
+def test_c2_full_direct_kernel(cf, oracle):
+    """BASELINE configs[1]: n = 1e6, f = 0.05, 3 robustness iterations, direct kernel."""
+    n, f, nsteps = 1_000_000, 0.05, 3
+    x = datagen.grid_x(n)
+    y = datagen.noisy_y(x)
+    fit = cf.lowess_smoothing()
+    fit.set_method("direct")
+    fit.initialize(x, y, srt=False)
+    ys = fit.smooth(f, nsteps=nsteps)
+    assert np.all(np.isfinite(ys)) and np.array_equal(fit.m_residuals, y - ys)
+    rw_in, ys0 = _check_robust_step(fit, f, y)
+    _teacher(fit, oracle, x, y, f, rw_in, ys0, 200)
+
+
+def test_c4_full_tree_and_linear_property(cf, oracle):
+    """BASELINE headline series: n = 1e8, f = 0.05, 3 robustness iterations (moment-tree
+    evaluator; the direct kernel needs > 15 min per smooth at this size)."""
+    n, f, nsteps = 100_000_000, 0.05, 3
+    x = datagen.grid_x(n)
+    # linearity first (cheap to state, exact to check): y = a + b x  ->  ys = y, rw = 1
+    y = 2.0 - 3.0 * x
+    fit = cf.lowess_smoothing()
+    fit.set_method("tree")
+    fit.initialize(x, y, srt=False)
+    ys = fit.smooth(f, nsteps=1)
+    assert np.max(np.abs(ys - y)) <= TOL * np.max(np.abs(y))
+    del ys
+    y = datagen.noisy_y(x)
+    fit.initialize(x, y, srt=False)
+    ys = fit.smooth(f, nsteps=nsteps)
+    assert np.all(np.isfinite(ys)) and np.array_equal(fit.m_residuals, y - ys)
+    del ys
+    rw_in, ys0 = _check_robust_step(fit, f, y)
+    _teacher(fit, oracle, x, y, f, rw_in, ys0, 36)
+
+
+def test_c5_full_wide_span_both_evaluators(cf, oracle):
+    """BASELINE configs[4]: n = 2e6, f = 0.8, 5 robustness iterations.  The whole smooth runs
+    on the tree; one weighted pass of the direct kernel (2 s) must agree with it and with
+    the oracle's samples."""
+    n, f, nsteps = 2_000_000, 0.8, 5
+    x = datagen.grid_x(n)
+    y = datagen.noisy_y(x)
+    fit = cf.lowess_smoothing()
+    fit.set_method("tree")
+    fit.initialize(x, y, srt=False)
+    ys = fit.smooth(f, nsteps=nsteps)
+    assert np.all(np.isfinite(ys))
+    rw_in, ys0 = _check_robust_step(fit, f, y)
+    _teacher(fit, oracle, x, y, f, rw_in, ys0, 48)
+    fit.set_method("direct")
+    ysd, _, _ = fit.run_from_rw(f, rw_in, passes=1)
+    assert cases.close(ysd, ys0, TOL)[0]
+    _teacher(fit, oracle, x, y, f, rw_in, ysd, 48)
+
+
+def test_c3_full_batched(cf, oracle):
+    """BASELINE configs[2]: 4096 independent series x n = 16384, f = 0.3 (nsteps = 2), through
+    the host-buffer batched entry point; four series are checked in full against the oracle,
+    every series by the bitwise residual identity and the weight bounds."""
+    s, n, f = 4096, 16384, 0.3
+    x1 = datagen.grid_x(n)
+    base = datagen.signal(x1)
+    x = np.broadcast_to(x1, (s, n)).copy()
+    y = np.empty((s, n))
+    for k in range(s):
+        y[k] = base + (datagen.uniform01(datagen.SEED_Y + (k << 32), n) - 0.5)
+    ys, rw, res = cf.cf_lowess_smooth_batched(x, y, f, 2)
+    assert np.all(np.isfinite(ys)) and np.array_equal(res, y - ys)
+    assert np.all((rw >= 0.0) & (rw <= 1.0))
+    for k in (0, 1, 2047, 4095):
+        ref = oracle.lowess_mt(x[k], y[k], f, 2)
+        ok, d, nref = cases.close_or_exact(ys[k], ref["ys"], x[k], y[k], rw[k], f, TOL)
+        assert ok, (k, d, nref)
+        assert np.max(np.abs(rw[k] - ref["rw"])) < 1e-9, k
