@@ -52,8 +52,7 @@ static void free_buffers(cf_lowess* h)
 {
     peer_detach(h);
     cudaFree(h->x); cudaFree(h->y); cudaFree(h->ys); cudaFree(h->rw); cudaFree(h->res);
-    cudaFree(h->win.nleft); cudaFree(h->win.lo9); cudaFree(h->win.hi9);
-    cudaFree(h->win.lo1); cudaFree(h->win.hi1); cudaFree(h->win.leader);
+    cudaFree(h->win.nleft);      // one block holds all six window arrays
     h->x = h->y = h->ys = h->rw = h->res = nullptr;
     h->win = Windows{};
     h->cap = h->cap_rw = 0;
@@ -79,12 +78,12 @@ static int reserve(cf_lowess* h, int32_t n, int32_t nseries = 1)
         CF_CUDA(cudaMalloc(&h->y, bd));
         CF_CUDA(cudaMalloc(&h->ys, bd));
         CF_CUDA(cudaMalloc(&h->res, bd));
-        CF_CUDA(cudaMalloc(&h->win.nleft, bi));
-        CF_CUDA(cudaMalloc(&h->win.lo9, bi));
-        CF_CUDA(cudaMalloc(&h->win.hi9, bi));
-        CF_CUDA(cudaMalloc(&h->win.lo1, bi));
-        CF_CUDA(cudaMalloc(&h->win.hi1, bi));
-        CF_CUDA(cudaMalloc(&h->win.leader, bi));
+        CF_CUDA(cudaMalloc(&h->win.nleft, 6 * bi));
+        h->win.lo9 = h->win.nleft + need;
+        h->win.hi9 = h->win.lo9 + need;
+        h->win.lo1 = h->win.hi9 + need;
+        h->win.hi1 = h->win.lo1 + need;
+        h->win.leader = h->win.hi1 + need;
         h->cap = need;
     }
     return CF_OK;
@@ -230,6 +229,7 @@ void cf_lowess_destroy(cf_lowess* h)
     cudaFree(h->hist);
     cudaFree(h->sel);
     cudaFree(h->span);
+    cudaFree(h->sort_aux);
     cudaFree(h->part);
     cudaFree(h->tree);
     delta_free(h);
@@ -258,7 +258,17 @@ static int32_t init_common(cf_lowess* h, const void* x, const void* y, int32_t n
             // stage the unsorted input in ys/res, sort into x/y  (:793-798)
             CF_CUDA(cudaMemcpyAsync(h->ys, x, bytes, kind, h->stream));
             CF_CUDA(cudaMemcpyAsync(h->res, y, bytes, kind, h->stream));
-            CF_TRY(sort_xy_device(h->ys, h->res, n, h->x, h->y, nullptr, h->stream, &h->launches));
+            // scratch: the (not yet computed) window arrays hold the key / index buffers
+            const size_t aux = sort_aux_bytes(n);
+            if (aux > h->sort_aux_cap) {
+                cudaFree(h->sort_aux);
+                h->sort_aux = nullptr;
+                h->sort_aux_cap = 0;
+                CF_CUDA(cudaMalloc(&h->sort_aux, aux));
+                h->sort_aux_cap = aux;
+            }
+            CF_TRY(sort_xy_inplace(h->ys, h->res, n, h->x, h->y, h->win.nleft, h->sort_aux, h->stream,
+                                   &h->launches));
         } else {
             CF_CUDA(cudaMemcpyAsync(h->x, x, bytes, kind, h->stream));   // :800-803
             CF_CUDA(cudaMemcpyAsync(h->y, y, bytes, kind, h->stream));

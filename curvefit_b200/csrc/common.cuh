@@ -127,7 +127,10 @@ struct cf_lowess {
     // device buffers (capacity in elements)
     int64_t cap = 0, cap_rw = 0;
     double *x = nullptr, *y = nullptr, *ys = nullptr, *rw = nullptr, *res = nullptr;
-    cf::Windows win = {};
+    cf::Windows win = {};   // six int32 arrays carved from ONE block (win.nleft = its start): the
+                            // block doubles as the radix sort's 24 n bytes of (key, index) buffers
+    void* sort_aux = nullptr;            // digit table of the sort, kept between calls
+    size_t sort_aux_cap = 0;
     double win_f = -1.0;  // span fraction the stored windows were built for
     int32_t ns = 0;
 
@@ -191,7 +194,11 @@ void peer_detach(cf_lowess* h);               // peer.cu
 
 // device radix sort of (x, index) ascending, y co-permuted; d_perm may be null
 int sort_xy_device(const double* d_x_in, const double* d_y_in, int32_t n, double* d_x_out,
-                   double* d_y_out, int32_t* d_perm_out, cudaStream_t s, int* launches);
+                   double* d_y_out, int32_t* d_perm_out, cudaStream_t s, int* launches,
+                   void* pairs = nullptr, void* aux = nullptr);
+size_t sort_aux_bytes(int32_t n);
+int sort_xy_inplace(double* x_io, double* y_io, int32_t n, double* x_out, double* y_out,
+                    void* scratch16n, void* aux, cudaStream_t s, int* launches);
 
 int fp64_peak(int device, double ms_target, double* tflops, double* mhz);
 
