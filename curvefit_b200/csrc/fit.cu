@@ -28,7 +28,11 @@
 // w = 1, r > h9 -> w = 0, sweep exit) are taken from the integer ranges of
 // windows.cu, never from the rounded q, so the set of contributing elements is
 // exactly the reference's.
+#include <cooperative_groups.h>
+
 #include "common.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace cf {
 
@@ -190,7 +194,10 @@ constexpr size_t fit_smem_bytes()
     return sizeof(double2) * 2 * 3 * (size_t)(NT * E) + sizeof(int32_t) * 4 * (size_t)(NT * P);
 }
 
-template <int NT, int P, int E, int MINB, int U>
+// CL (opt-in, see launch_variant): the K <= 8 CTAs of a tile form a thread-block CLUSTER and
+// add their partial moments through distributed shared memory in part order.  Default: the
+// parts go through prm.part and fit_finalize_kernel.
+template <int NT, int P, int E, int MINB, int U, bool CL>
 __global__ void __launch_bounds__(NT, MINB)
 fit_kernel(const FitParams prm_in)
 {
@@ -214,7 +221,7 @@ fit_kernel(const FitParams prm_in)
     Tile<NT, P> t;
     tile_setup<NT, P>(prm, tile0, t, rng, ts);
     const int jlo = t.jlo, jhi = t.jhi;
-    if (jlo > jhi) return;                     // tile holds tie followers only
+    if (!CL && jlo > jhi) return;              // tile holds tie followers only (a cluster stays for its barriers)
     const double xc = t.xc, sc = t.sc;
     const bool exact = t.exact;
 
@@ -258,7 +265,7 @@ fit_kernel(const FitParams prm_in)
         }
     };
 
-    const int nch = (jhi - jlo) / C + 1;
+    const int nch = jlo > jhi ? 0 : (jhi - jlo) / C + 1;
     const int k0 = (int)(((long long)nch * part) / K);
     const int k1 = (int)(((long long)nch * (part + 1)) / K);
     if (k0 < k1) {
@@ -370,6 +377,45 @@ fit_kernel(const FitParams prm_in)
         __syncthreads();
     }
 
+    if (CL) {
+        // Every CTA parks its partial moments in its own shared memory (the staging
+        // buffers are free now); CTA 0 of the cluster adds the K parts in part order
+        // (= ascending j, the same order as fit_finalize_kernel) over DSMEM.
+        cg::cluster_group cluster = cg::this_cluster();
+        double* mine = reinterpret_cast<double*>(smem_raw);          // [5][T] <= 2*3*C double2
+        static_assert(sizeof(double) * 5 * T <= sizeof(double2) * 2 * 3 * C, "partials must fit the staging buffers");
+        __syncthreads();
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            const int loc = wid * (32 * P) + p * 32 + lane;
+            mine[0 * T + loc] = S0[p];
+            mine[1 * T + loc] = S1[p];
+            mine[2 * T + loc] = S2[p];
+            mine[3 * T + loc] = T0[p];
+            mine[4 * T + loc] = T1[p];
+        }
+        cluster.sync();
+        if (part == 0 && jlo <= jhi) {
+            const double range = x[prm.n - 1] - x[0];
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                if (!t.valid[p]) continue;
+                const int loc = wid * (32 * P) + p * 32 + lane;
+                double m[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+                for (int k = 0; k < K; ++k) {
+                    const double* src = cluster.map_shared_rank(mine, k);
+#pragma unroll
+                    for (int q = 0; q < 5; ++q) m[q] += src[q * T + loc];
+                }
+                const int32_t i = slot_point(prm, tile0 + loc);
+                const double scale = exact ? t.hp[p] : t.hc;
+                const double us = exact ? 0.0 : (t.xsp[p] - xc) * sc;
+                prm.ys[i] = fit_value(m[0], m[1], m[2], m[3], m[4], y[i], t.hp[p], scale, us, range);
+            }
+        }
+        cluster.sync();                       // nobody leaves while CTA 0 still reads its memory
+        return;
+    }
     if (K > 1) {
         // partial moments; fit_finalize_kernel adds the K parts in part order
         double* __restrict__ dst = prm.part + ((size_t)tile * K + part) * (5 * (size_t)T);
@@ -441,12 +487,10 @@ int launch_variant(cf_lowess* h, FitParams& prm, int sms)
 {
     constexpr int T = NT * P, C = NT * E;
     constexpr size_t smem = fit_smem_bytes<NT, P, E>();
-    auto kern = fit_kernel<NT, P, E, MINB, U>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        CF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_set = true;
-    }
+    auto kern = fit_kernel<NT, P, E, MINB, U, false>;
+    auto kern_cl = fit_kernel<NT, P, E, MINB, U, true>;
+    CF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CF_CUDA(cudaFuncSetAttribute(kern_cl, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int tiles = (prm.end - prm.begin + T - 1) / T;
     const long long all_tiles = (long long)tiles * h->nseries;
     prm.tiles = tiles;
@@ -465,8 +509,32 @@ int launch_variant(cf_lowess* h, FitParams& prm, int sms)
     if (K > maxk) K = maxk;
     if (K > 64) K = 64;
     if (K < 1) K = 1;
+    // CF_FIT_VARIANT=4 (development): K <= 8 parts as one thread-block cluster that adds its
+    // partial moments through DSMEM -- no scratch in HBM, no second kernel.  Measured on B200
+    // at n = 1e6, ns = 5e4: 34.7 ms per pass against 32.7 ms for the scratch path (cluster
+    // placement costs more than the 0.4 GB of partial-moment traffic it saves), so it is off.
+    if (h->fit_variant == 4 && K > 8) K = 8;
+    const bool use_cluster = h->fit_variant == 4 && K > 1 && K <= 8;
     prm.ksplit = K;
     prm.part = nullptr;
+    if (use_cluster) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(tiles * K, h->nseries);
+        cfg.blockDim = dim3(NT);
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = h->stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = K;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        CF_CUDA(cudaLaunchKernelEx(&cfg, kern_cl, prm));
+        h->launches++;
+        h->fit_launches++;
+        return CF_OK;
+    }
     if (K > 1) {
         const size_t need = (size_t)all_tiles * K * 5 * T * sizeof(double);
         if (need > h->part_bytes) {

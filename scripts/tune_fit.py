@@ -16,8 +16,9 @@ def main():
     y = datagen.noisy_y(x)
     ns = int(f * n)
     print("fp64 peak", regression.fp64_peak(-1, 200.0))
-    for variant in (0, 6, 7, 8, 9):
-        for ks in (0, 16):
+    # variant 4: cluster/DSMEM reduction (K <= 8); 0: partial moments through HBM
+    for variant, ks in [(4, 0), (4, 2), (4, 4), (4, 8), (0, 0), (0, 4), (0, 6), (0, 8), (0, 10), (0, 12), (0, 16)]:
+        if True:
             os.environ["CF_FIT_VARIANT"] = str(variant)
             os.environ["CF_FIT_KSPLIT"] = str(ks)
             fit = lowess_smoothing()
