@@ -333,8 +333,11 @@ __device__ __forceinline__ void take_core(const double* __restrict__ nd, double 
 //   1. tricube nodes of [lo9, lo1) and (hi1, hi9]   (~110 FP64 instr each)
 //   2. core nodes of [lo1, hi1]                     (~15)
 //   3. the < 16 elements at either end of each range, reference formula (~13 each)
-template <int NT>
-__global__ void __launch_bounds__(NT)
+// (Tried and dropped, B200, n = 1e8: a one-node-ahead prefetch, splitting the phases into
+// two kernels, advancing the left and right walks together -- all within 2 % or slower;
+// occupancy below 5 CTAs of 128 threads per SM costs 10-40 %.)
+template <int NT, int MINB>
+__global__ void __launch_bounds__(NT, MINB)
 tree_eval_kernel(const TreeParams prm)
 {
     const size_t soff = (size_t)blockIdx.y * (size_t)prm.n;
@@ -413,41 +416,44 @@ tree_eval_kernel(const TreeParams prm)
     }
     // ---- phase 3: range ends, element by element (:542-556 per pair)
     {
-        // adjacent pieces are merged: [l9,hdL) | [tlL,l1)+[l1,hdC) | [tlC,r1+1)+[r1+1,hdR) | [tlR,r9+1)
-        int32_t sa[4], sb[4];
-        sa[0] = l9;  sb[0] = hdL;
-        sa[1] = tlL; sb[1] = hdC;
-        sa[2] = tlC; sb[2] = hdR;
-        sa[3] = tlR; sb[3] = r9 + 1;
-        int seg = 0;
-        int32_t j = sa[0], je = sb[0];
-        auto settle = [&]() -> bool {
-            while (j >= je) {
-                if (++seg > 3) return false;
-                j = seg == 1 ? sa[1] : seg == 2 ? sa[2] : sa[3];
-                je = seg == 1 ? sb[1] : seg == 2 ? sb[2] : sb[3];
-            }
-            return true;
+        // adjacent pieces are merged: [l9,hdL) | [tlL,l1)+[l1,hdC) | [tlC,r1+1)+[r1+1,hdR) | [tlR,r9+1).
+        // Two independent streams per lane -- A: pieces 1, 2 (left of the core), B: pieces 3, 4 --
+        // with their own accumulators: half the trip count and two dependency chains in flight.
+        int32_t ja = l9, ea = hdL, jb = tlC, eb = hdR;
+        bool a2 = false, b2 = false;
+        auto settle_a = [&]() -> bool {
+            if (ja >= ea && !a2) { a2 = true; ja = tlL; ea = hdC; }
+            return ja < ea;
         };
-        bool have = valid && settle();
-        while (__any_sync(kFull, have)) {
-            if (have) {
-                const double q = (x[j] - xs) * invh;
-                const double tt = fma(-(q * q), fabs(q), 1.0);
-                double wgt = (tt * tt) * tt;
-                wgt = (j >= l1 && j <= r1) ? 1.0 : wgt;             // :547-551
-                const double wr = rw ? wgt * rw[j] : wgt;
-                const double wq = wr * q;
-                const double yj = y[j];
-                m.S0 += wr;
-                m.S1 += wq;
-                m.S2 = fma(wq, q, m.S2);
-                m.T0 = fma(wr, yj, m.T0);
-                m.T1 = fma(wq, yj, m.T1);
-                ++j;
-                have = settle();
-            }
+        auto settle_b = [&]() -> bool {
+            if (jb >= eb && !b2) { b2 = true; jb = tlR; eb = r9 + 1; }
+            return jb < eb;
+        };
+        bool ha = valid && settle_a(), hb = valid && settle_b();
+        Moments mb = {0.0, 0.0, 0.0, 0.0, 0.0};
+        auto pair = [&](int32_t j, bool on, Moments& acc) {
+            const double q = (x[j] - xs) * invh;
+            const double tt = fma(-(q * q), fabs(q), 1.0);
+            double wgt = (tt * tt) * tt;
+            wgt = (j >= l1 && j <= r1) ? 1.0 : wgt;                 // :547-551
+            wgt = on ? wgt : 0.0;
+            const double wr = rw ? wgt * rw[j] : wgt;
+            const double wq = wr * q;
+            const double yj = y[j];
+            acc.S0 += wr;
+            acc.S1 += wq;
+            acc.S2 = fma(wq, q, acc.S2);
+            acc.T0 = fma(wr, yj, acc.T0);
+            acc.T1 = fma(wq, yj, acc.T1);
+        };
+        const int32_t safe = valid ? i : 0;
+        while (__any_sync(kFull, ha || hb)) {
+            pair(ha ? ja : safe, ha, m);
+            pair(hb ? jb : safe, hb, mb);
+            if (ha) { ++ja; ha = settle_a(); }
+            if (hb) { ++jb; hb = settle_b(); }
         }
+        m.S0 += mb.S0; m.S1 += mb.S1; m.S2 += mb.S2; m.T0 += mb.T0; m.T1 += mb.T1;
     }
     if (valid) {
         const double range = x[prm.n - 1] - x[0];                          // :535
@@ -502,9 +508,8 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
         CF_CUDA(cudaGetLastError());
         h->launches++;
     }
-    constexpr int NT = 128;
     const int cntp = prm.end - prm.begin;
-    tree_eval_kernel<NT><<<dim3((cntp + NT - 1) / NT, h->nseries), NT, 0, h->stream>>>(prm);
+    tree_eval_kernel<128, 5><<<dim3((cntp + 127) / 128, h->nseries), 128, 0, h->stream>>>(prm);
     CF_CUDA(cudaGetLastError());
     h->launches++;
     h->fit_launches++;
