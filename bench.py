@@ -51,8 +51,8 @@ FLOP_PER_PAIR = 17.0
 # dram__bytes_read.sum + dram__bytes_write.sum of one fit_kernel launch, from the committed
 # `ncu --set full` captures (profiles/README.md); None where no capture exists.
 NCU_TRAFFIC = {
-    "c2": {"bytes": 53.1e6 + 349.3e6, "from": "profiles/r01_fit_kernel_c2_ncu_full.csv (K=10 window split "
-                                              "writes 400 MB of partial moments; 0.15% of DRAM peak)"},
+    "c2": {"bytes": 48.5e6 + 349.2e6, "from": "profiles/r01_fit_kernel_c2_ncu_full.csv (mean of 2 launches; K=10 "
+                                              "window split writes 400 MB of partial moments; 0.15% of DRAM peak)"},
 }
 BYTES_PER_POINT_PASS = 56.0
 
