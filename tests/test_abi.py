@@ -96,3 +96,35 @@ def test_host_side_error_behaviour_mirrors_reference():
     with pytest.raises(core.CurvefitError) as ei:
         lowess_smoothing().smooth(0.5)
     assert ei.value.flag == 300
+
+
+def test_moving_average_and_median_host_checks_need_no_device():
+    """moving_average_1's input check (:452-457) and median's n = 0 / srt = .false. paths
+    (src/curvefit_statistics.f90:280-293) are host logic; the device entry points fail loudly
+    without a GPU."""
+    import curvefit_b200 as cf
+    x = np.arange(6.0)
+    for npts in (1, 7):
+        err = errors()
+        err.set_exit_on_error(False)
+        err.set_suppress_printing(True)
+        cf.moving_average(x, npts, err=err)
+        assert err.get_error_flag() == core.CF_INVALID_INPUT_ERROR
+        assert err.get_error_fcn_name() == "moving_average_1"
+    assert np.array_equal(x, np.arange(6.0))
+    with pytest.raises(core.CurvefitError):
+        cf.moving_average(x, 1)                      # default error object "terminates"
+    assert cf.median(np.zeros(0)) == 0.0
+    assert cf.median(np.array([1.0, 2.0, 4.0, 8.0]), srt=False) == 3.0
+    assert cf.median(np.array([1.0, 2.0, 4.0]), srt=False) == 2.0
+    lib = _lib.load()
+    assert lib.cf_moving_average(x.ctypes.data_as(_lib.c_dp), 6, 1) == core.CF_INVALID_INPUT_ERROR
+    if not _have_gpu():
+        assert lib.cf_moving_average(x.ctypes.data_as(_lib.c_dp), 6, 3) == core.CF_DEVICE_ERROR
+        z = C.c_double()
+        assert lib.cf_median(x.ctypes.data_as(_lib.c_dp), 6, C.byref(z)) == core.CF_DEVICE_ERROR
+        out = np.zeros(6)
+        assert lib.cf_sort(x.ctypes.data_as(_lib.c_dp), 6, out.ctypes.data_as(_lib.c_dp)) == core.CF_DEVICE_ERROR
+        assert lib.cf_lowess_smooth_delta(x.ctypes.data_as(_lib.c_dp), x.ctypes.data_as(_lib.c_dp), 6, 0.5, 2, 0.1,
+                                          out.ctypes.data_as(_lib.c_dp), out.ctypes.data_as(_lib.c_dp),
+                                          out.ctypes.data_as(_lib.c_dp)) == core.CF_DEVICE_ERROR
