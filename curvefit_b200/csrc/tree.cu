@@ -39,6 +39,8 @@
 //
 // This backend is separate from fit.cu (the direct kernel that carries the
 // FP64 roofline claim); cf_lowess_set_method() selects it.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace cf {
@@ -47,6 +49,7 @@ constexpr int kLeaf = 16;       // elements per leaf
 constexpr int kNodeLen = 32;    // doubles per node: c, d, A[12], B[11], pad
 constexpr int kKA = 12, kKB = 11;
 constexpr int kMaxLevels = 30;
+constexpr int kMaxGroups = 4;              // chain levels
 
 struct TreeParams {
     const double* x;
@@ -63,7 +66,9 @@ struct TreeParams {
     int64_t off[kMaxLevels];    // first node of the level
     int64_t total;              // nodes per series (binary tree + chains)
     int32_t ngroups;            // chain levels g = 1 .. ngroups
-    int64_t coff[9];            // coff[g]: first SUF_g node; PRE_g follows after cnt[4(g-1)] nodes
+    int32_t cbits[kMaxGroups + 1];   // chain level g groups 2^cbits[g] units into a block
+    int32_t ulev[kMaxGroups + 2];    // its units are the binary nodes of level ulev[g]; ulev[g+1] = ulev[g] + cbits[g]
+    int64_t coff[kMaxGroups + 1];    // coff[g]: first SUF_g node; PRE_g follows after cnt[ulev[g]] nodes
 };
 
 __device__ __forceinline__ double2 ld2(const double* p)
@@ -289,14 +294,15 @@ struct Walk {
 __global__ void __launch_bounds__(128)
 tree_chain_kernel(const TreeParams prm, int g)
 {
-    const int ulev = 4 * (g - 1);
+    const int ulev = prm.ulev[g];
+    const int32_t cm = (1 << prm.cbits[g]) - 1;
     const int32_t ucnt = prm.cnt[ulev];
     const int32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
     const int32_t t = tid >> 1;
     const int dir = tid & 1;
     if (t >= ucnt) return;
     const int series = blockIdx.y;
-    const int32_t t0 = t & ~15, t1 = min(t0 + 16, ucnt);
+    const int32_t t0 = t & ~cm, t1 = min(t0 + cm + 1, ucnt);
     const int32_t ra = dir == 0 ? t0 : t, rb = dir == 0 ? t + 1 : t1;     // units [ra, rb)
     {   // only what the windows of this shard can reach
         int32_t j0, j1, k0, k1;
@@ -326,31 +332,34 @@ tree_chain_kernel(const TreeParams prm, int g)
 // ends share a block.  Yields node indices into TreeParams::nodes.
 struct Chain {
     int32_t a, b;
-    int g, stage;
+    int g, stage, cb;
     bool tail;
     Walk w;
     __device__ __forceinline__ void start(int32_t la, int32_t lb)
     {
-        a = la; b = lb; g = 1; stage = 0; tail = false;
+        a = la; b = lb; g = 1; stage = 0; cb = 0; tail = false;
         if (a >= b) { a = b = 0; tail = true; w.start(0, 0); }
     }
     __device__ __forceinline__ bool next(const TreeParams& prm, int64_t& node)
     {
         while (!tail) {
             if (stage == 0) {
-                if (g > prm.ngroups || (a >> 4) == ((b - 1) >> 4)) {
+                cb = g <= prm.ngroups ? prm.cbits[g] : 0;
+                if (cb == 0 || (a >> cb) == ((b - 1) >> cb)) {
                     tail = true;
-                    w.start_at(a, b, 4 * (g - 1));
+                    w.start_at(a, b, prm.ulev[min(g, prm.ngroups + 1)]);
                     break;
                 }
                 stage = 1;
-                if (a & 15) { node = prm.coff[g] + a; a = (a | 15) + 1; return true; }
+                const int32_t cm = (1 << cb) - 1;
+                if (a & cm) { node = prm.coff[g] + a; a = (a | cm) + 1; return true; }
             }
             if (stage == 1) {
                 stage = 2;
-                if (b & 15) { node = prm.coff[g] + prm.cnt[4 * (g - 1)] + (b - 1); b &= ~15; return true; }
+                const int32_t cm = (1 << cb) - 1;
+                if (b & cm) { node = prm.coff[g] + prm.cnt[prm.ulev[g]] + (b - 1); b &= ~cm; return true; }
             }
-            a >>= 4; b >>= 4; ++g; stage = 0;
+            a >>= cb; b >>= cb; ++g; stage = 0;
             if (a >= b) { tail = true; w.start(0, 0); return false; }
         }
         int lv;
@@ -609,10 +618,40 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
     prm.nlevels = L;
     // chains: level g groups the units of binary level 4(g-1) in blocks of 16
     prm.ngroups = 0;
-    for (int g = 1; g <= 8 && 4 * (g - 1) < L && prm.cnt[4 * (g - 1)] > 16; ++g) {
-        prm.coff[g] = total;
-        total += 2 * (int64_t)prm.cnt[4 * (g - 1)];
-        prm.ngroups = g;
+    {
+        // Geometry: a side range holds about ns/2 elements = R leaves.  The chain levels
+        // together climb T = log2(R) - 1 binary levels (so that the top units are R/2..R/4
+        // leaves and what is left for the binary walk is 2-4 units), split evenly over as
+        // few levels as keep a block at <= 2^9 units.
+        int bits[kMaxGroups + 1] = {0, 0, 0, 0, 0};
+        int G = 0;
+        int T = 0;
+        for (int64_t r = (int64_t)h->ns / (2 * kLeaf); r > 1; r >>= 1) ++T;
+        T -= 1;
+        if (T >= 3) {
+            G = (T + 8) / 9;
+            if (G > kMaxGroups) G = kMaxGroups;
+            for (int g = 1; g <= G; ++g) bits[g] = T / G + (g <= T % G ? 1 : 0);
+            for (int g = 1; g <= G; ++g) if (bits[g] > 9) bits[g] = 9;
+        }
+        if (const char* v = getenv("CF_TREE_BITS")) {        // development: "8,8" etc.
+            G = 0;
+            while (*v && G < kMaxGroups) {
+                bits[++G] = atoi(v);
+                while (*v && *v != ',') ++v;
+                if (*v == ',') ++v;
+            }
+        }
+        prm.ulev[1] = 0;
+        for (int g = 1; g <= G; ++g) {
+            const int ul = prm.ulev[g];
+            if (bits[g] < 1 || ul >= L || prm.cnt[ul] <= (1 << bits[g])) break;
+            prm.cbits[g] = bits[g];
+            prm.ulev[g + 1] = ul + bits[g];
+            prm.coff[g] = total;
+            total += 2 * (int64_t)prm.cnt[ul];
+            prm.ngroups = g;
+        }
     }
     prm.total = total;
     const size_t need = sizeof(double) * kNodeLen * (size_t)total * (size_t)h->nseries;
@@ -641,7 +680,7 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
         h->launches++;
     }
     for (int g = 1; g <= prm.ngroups; ++g) {
-        const int32_t ucnt = prm.cnt[4 * (g - 1)];
+        const int32_t ucnt = prm.cnt[prm.ulev[g]];
         tree_chain_kernel<<<dim3((2 * ucnt + 127) / 128, h->nseries), 128, 0, h->stream>>>(prm, g);
         CF_CUDA(cudaGetLastError());
         h->launches++;
