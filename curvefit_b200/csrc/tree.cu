@@ -628,7 +628,9 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
         int T = 0;
         for (int64_t r = (int64_t)h->ns / (2 * kLeaf); r > 1; r >>= 1) ++T;
         T -= 1;
-        if (T >= 3) {
+        // delta > 0 with few fitted points: the chains would cost more to build than they save
+        const bool sparse = h->delta > 0.0 && (int64_t)h->nfit * 64 < (int64_t)h->n;
+        if (T >= 3 && !sparse) {
             G = (T + 8) / 9;
             if (G > kMaxGroups) G = kMaxGroups;
             for (int g = 1; g <= G; ++g) bits[g] = T / G + (g <= T % G ? 1 : 0);
