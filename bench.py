@@ -405,6 +405,24 @@ def tree_numbers(args, fit, flush, x, y, f, nsteps):
     out["same_workload"] = {"value": x.size / (ms * 1e-3), "unit": "points/s", "ms_per_step": ms,
                             "max_abs_diff_vs_direct": float(np.max(np.abs(ys_tree - ys_direct))),
                             "max_abs_ys": float(np.max(np.abs(ys_direct)))}
+    if not args.no_e2e:
+        # the same host-buffer C ABI call as `e2e`, with CF_LOWESS_METHOD=tree
+        from curvefit_b200 import regression
+        xp = torch.from_numpy(x).pin_memory().numpy()
+        yp = torch.from_numpy(y).pin_memory().numpy()
+        outs = tuple(torch.empty(x.size, dtype=torch.float64).pin_memory().numpy() for _ in range(3))
+        os.environ["CF_LOWESS_METHOD"] = "tree"
+        try:
+            regression.cf_lowess_smooth(xp, yp, f, nsteps, out=outs)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(5):
+                regression.cf_lowess_smooth(xp, yp, f, nsteps, out=outs)
+            dt = (time.perf_counter() - t0) / 5
+        finally:
+            os.environ.pop("CF_LOWESS_METHOD", None)
+        out["same_workload"]["e2e"] = {"value": x.size / dt, "unit": "points/s", "ms_per_step": dt * 1e3,
+                                       "h2d_bytes_per_step": 16 * x.size, "d2h_bytes_per_step": 24 * x.size}
     n4, f4, k4, name4 = WORKLOADS["c4"]
     if x.size != n4:
         x4, y4 = make_data(n4)

@@ -142,6 +142,16 @@ static int begin_stage(cf_lowess* h, double f)
     return CF_OK;
 }
 
+// CF_LOWESS_METHOD = direct | tree | auto (default direct)
+static int method_from_env()
+{
+    const char* v = getenv("CF_LOWESS_METHOD");
+    if (!v) return CF_METHOD_DIRECT;
+    if (!strcmp(v, "tree")) return CF_METHOD_TREE;
+    if (!strcmp(v, "auto")) return CF_METHOD_AUTO;
+    return CF_METHOD_DIRECT;
+}
+
 }  // namespace cf
 
 using namespace cf;
@@ -195,11 +205,7 @@ int32_t cf_lowess_create(cf_lowess** out, int32_t device, void* stream)
     h->device = device;
     if (const char* v = getenv("CF_FIT_VARIANT")) h->fit_variant = atoi(v);
     if (const char* v = getenv("CF_FIT_KSPLIT")) h->ksplit_override = atoi(v);
-    if (const char* v = getenv("CF_LOWESS_METHOD")) {
-        if (!strcmp(v, "tree")) h->method = CF_METHOD_TREE;
-        else if (!strcmp(v, "auto")) h->method = CF_METHOD_AUTO;
-        else h->method = CF_METHOD_DIRECT;
-    }
+    h->method = method_from_env();
     if (stream) {
         h->stream = (cudaStream_t)stream;
     } else {
@@ -640,6 +646,7 @@ static int32_t pool_acquire(cf_lowess** out)
             if (g_pool[k]->device == dev) {
                 *out = g_pool[k];
                 g_pool.erase(g_pool.begin() + (long)k);
+                (*out)->method = method_from_env();     // the stateless calls follow the environment
                 return CF_OK;
             }
         }

@@ -172,7 +172,8 @@ CF_API int32_t cf_lowess_shard(const cf_lowess* h, int32_t* begin, int32_t* end,
  *                    relative measured; contract 1e-10);
  *  CF_METHOD_AUTO    tree when ns >= 1024, else direct.
  * Default: CF_METHOD_DIRECT, or the environment variable CF_LOWESS_METHOD
- * (direct | tree | auto) read at cf_lowess_create. */
+ * (direct | tree | auto), read at cf_lowess_create and by every stateless call
+ * (cf_lowess_smooth, cf_lowess_smooth_delta). */
 #define CF_METHOD_DIRECT 0
 #define CF_METHOD_TREE 1
 #define CF_METHOD_AUTO 2
