@@ -289,10 +289,10 @@ struct Walk {
     }
 };
 
-// One thread per (unit t, direction): PRE_g[t] / SUF_g[t] = the <= 4 binary nodes that tile
-// the units from the block's start to t / from t to the block's end, merged into one node.
+// Small levels (too few units to fill the GPU with segments): one thread per (unit t,
+// direction), PRE_g[t] / SUF_g[t] merged from the few aligned binary nodes that tile it.
 __global__ void __launch_bounds__(128)
-tree_chain_kernel(const TreeParams prm, int g)
+tree_chain_entry_kernel(const TreeParams prm, int g)
 {
     const int ulev = prm.ulev[g];
     const int32_t cm = (1 << prm.cbits[g]) - 1;
@@ -325,6 +325,64 @@ tree_chain_kernel(const TreeParams prm, int g)
         acc = nx;
     }
     node_store(out, acc);
+}
+
+// One thread per (segment of <= 16 units, direction).  PRE: the units from the block's start
+// up to the segment come from the binary tree (<= a few aligned nodes), then the segment is
+// swept left to right, one merge and one stored node per unit; SUF mirrors it.
+constexpr int kChainSeg = 16;
+
+__global__ void __launch_bounds__(128)
+tree_chain_kernel(const TreeParams prm, int g)
+{
+    const int ulev = prm.ulev[g];
+    const int32_t cm = (1 << prm.cbits[g]) - 1;
+    const int32_t ucnt = prm.cnt[ulev];
+    const int32_t seg = min(kChainSeg, cm + 1);                              // never across blocks
+    const int32_t nseg = (ucnt + seg - 1) / seg;
+    const int32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+    const int32_t sg = tid >> 1;
+    const int dir = tid & 1;
+    if (sg >= nseg) return;
+    const int series = blockIdx.y;
+    const int32_t s0 = sg * seg, s1 = min(s0 + seg, ucnt);                  // units [s0, s1)
+    const int32_t t0 = s0 & ~cm, t1 = min(t0 + cm + 1, ucnt);               // their block
+    {   // only what the windows of this shard can reach
+        int32_t j0, j1, k0, k1;
+        node_span(ulev, s0, prm.n, j0, k0);
+        node_span(ulev, s1 - 1, prm.n, k1, j1);
+        const int32_t lo = __ldg(prm.span + 2 * series), hi = __ldg(prm.span + 2 * series + 1);
+        if (j1 < lo || j0 > hi) return;
+    }
+    double* base = prm.nodes + (size_t)series * prm.total * kNodeLen;
+    const double* units = base + prm.off[ulev] * kNodeLen;
+    double* suf = base + prm.coff[g] * kNodeLen;
+    double* pre = suf + (size_t)ucnt * kNodeLen;
+    NodeRegs acc, u, nx;
+    bool have = false;
+    {   // what lies between the block's edge and the segment
+        Walk w;
+        if (dir == 0) w.start_at(t0, s0, ulev); else w.start_at(s1, t1, ulev);
+        int lv;
+        int32_t idx;
+        while (w.next(lv, idx)) {
+            node_load(base + (prm.off[lv] + idx) * kNodeLen, u);
+            if (have) { node_merge(acc, u, nx); acc = nx; } else { acc = u; have = true; }
+        }
+    }
+    if (dir == 0) {
+        for (int32_t t = s0; t < s1; ++t) {
+            node_load(units + (size_t)t * kNodeLen, u);
+            if (have) { node_merge(acc, u, nx); acc = nx; } else { acc = u; have = true; }
+            node_store(pre + (size_t)t * kNodeLen, acc);
+        }
+    } else {
+        for (int32_t t = s1 - 1; t >= s0; --t) {
+            node_load(units + (size_t)t * kNodeLen, u);
+            if (have) { node_merge(acc, u, nx); acc = nx; } else { acc = u; have = true; }
+            node_store(suf + (size_t)t * kNodeLen, acc);
+        }
+    }
 }
 
 // The nodes that tile the leaf range [la, lb): per chain level at most one suffix node (left
@@ -683,7 +741,12 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
     }
     for (int g = 1; g <= prm.ngroups; ++g) {
         const int32_t ucnt = prm.cnt[prm.ulev[g]];
-        tree_chain_kernel<<<dim3((2 * ucnt + 127) / 128, h->nseries), 128, 0, h->stream>>>(prm, g);
+        const int32_t seg = (1 << prm.cbits[g]) < kChainSeg ? (1 << prm.cbits[g]) : kChainSeg;
+        const int32_t nseg = (ucnt + seg - 1) / seg;
+        if ((int64_t)nseg * h->nseries >= 65536)      // enough segments to fill the GPU: 1 merge per entry
+            tree_chain_kernel<<<dim3((2 * nseg + 127) / 128, h->nseries), 128, 0, h->stream>>>(prm, g);
+        else                                          // short critical path instead
+            tree_chain_entry_kernel<<<dim3((2 * ucnt + 127) / 128, h->nseries), 128, 0, h->stream>>>(prm, g);
         CF_CUDA(cudaGetLastError());
         h->launches++;
     }
