@@ -58,6 +58,17 @@ __device__ __forceinline__ double ordered_value(unsigned long long k)
     return __longlong_as_double((long long)b);
 }
 
+// bisquare robustness weight (:704-713), IEEE operations in the reference's order
+__device__ __forceinline__ double bisquare_weight(double res, double cmad, double c1, double c9)
+{
+    const double r = fabs(res);
+    if (r <= c1) return 1.0;
+    if (r > c9) return 0.0;
+    const double t = __ddiv_rn(r, cmad);
+    const double u = __dsub_rn(1.0, __dmul_rn(t, t));
+    return __dmul_rn(u, u);
+}
+
 // local linear fit evaluated at xs from the five moments (:559-584)
 __device__ __forceinline__ double fit_value(double S0, double S1, double S2, double T0, double T1,
                                             double yi, double h, double scale, double us,

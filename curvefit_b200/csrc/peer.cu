@@ -12,8 +12,8 @@
 //     [min lo9, max hi9] of its shard's windows once per smooth (peer_spans_kernel) --
 //     followed by peer_barrier_kernel so that no rank starts the next fit pass before
 //     its halo has landed;
-//   * peer_gather_kernel replicates the own block of ys / res / rw on every rank at
-//     the end (the full-length result of smooth()).
+//   * peer_gather_kernel stores the own block of ys (and rw, when asked for) into every
+//     rank at the end; res of the other blocks is completed locally (every rank holds y).
 //
 // Memory is shared between the one-process-per-GPU ranks with CUDA IPC handles
 // (cf_lowess_peer_export / _attach; the host runtime moves the 64-byte handles, e.g.
@@ -53,22 +53,33 @@ peer_spans_kernel(const PeerPtrs pp, const int32_t* __restrict__ span, unsigned 
     }
 }
 
-// own block [begin, end) of ys / res / rw (bits 0 / 1 / 2 of `what`) -> the same
-// positions on every other rank
+// own block [begin, end) of ys (and, if wanted, of rw -- the weights of the LAST robustness
+// iteration, which are not a function of the final residuals) -> the same positions on
+// every other rank.  res does not cross NVLink: every rank holds all of y and completes
+// res = y - ys (:695) for the other blocks itself (peer_complete_kernel), bit-identically.
 __global__ void __launch_bounds__(256)
 peer_gather_kernel(const PeerPtrs pp, int32_t begin, int32_t end, int what)
 {
     const int32_t i = begin + blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= end) return;
-    const double v = pp.ys[pp.rank][i], r = pp.res[pp.rank][i], w = pp.rw[pp.rank][i];
+    const double v = pp.ys[pp.rank][i], w = pp.rw[pp.rank][i];
 #pragma unroll
     for (int p = 0; p < kMaxPeers; ++p) {
         if (p < pp.nranks && p != pp.rank) {
-            if (what & 1) pp.ys[p][i] = v;
-            if (what & 2) pp.res[p][i] = r;
-            if (what & 4) pp.rw[p][i] = w;
+            pp.ys[p][i] = v;
+            if (what & CF_GATHER_RW) pp.rw[p][i] = w;
         }
     }
+}
+
+__global__ void __launch_bounds__(256)
+peer_complete_kernel(const double* __restrict__ y, const double* __restrict__ ys, double* __restrict__ res,
+                     int32_t begin, int32_t end, int32_t n)
+{
+    int32_t i = blockIdx.x * blockDim.x + threadIdx.x;       // index among the points NOT in [begin, end)
+    if (i >= begin) i += end - begin;
+    if (i >= n) return;
+    res[i] = __dsub_rn(y[i], ys[i]);
 }
 
 int launch_peer_barrier(cf_lowess* h)
@@ -98,7 +109,15 @@ int launch_peer_gather(cf_lowess* h, int what)
         CF_CUDA(cudaGetLastError());
         h->launches++;
     }
-    return launch_peer_barrier(h);
+    CF_TRY(launch_peer_barrier(h));
+    const int rest = h->n - cnt;
+    if (rest > 0 && (what & CF_GATHER_RES)) {
+        peer_complete_kernel<<<(rest + 255) / 256, 256, 0, h->stream>>>(h->y, h->ys, h->res, h->begin, h->end,
+                                                                        h->n);
+        CF_CUDA(cudaGetLastError());
+        h->launches++;
+    }
+    return CF_OK;
 }
 
 void peer_detach(cf_lowess* h)

@@ -203,15 +203,7 @@ bisquare_kernel(const double* __restrict__ res, double* __restrict__ rw,
     const size_t off = (size_t)blockIdx.y * (size_t)n;
     res += off; rw += off; st += blockIdx.y;
     const double cmad = st->cmad, c1 = st->c1, c9 = st->c9;
-    const double r = fabs(res[i]);
-    double w;
-    if (r <= c1) w = 1.0;
-    else if (r > c9) w = 0.0;
-    else {
-        const double t = __ddiv_rn(r, cmad);
-        const double u = __dsub_rn(1.0, __dmul_rn(t, t));
-        w = __dmul_rn(u, u);
-    }
+    const double w = bisquare_weight(res[i], cmad, c1, c9);
     rw[i] = w;
     if (PEER) {
         // halo exchange: only ranks whose windows reach element i get it

@@ -202,7 +202,7 @@ class ShardedLowess:
         the result.  The series length must not change while peers are attached."""
         s = self.s
         s.upload(x, y)
-        self.run(f, nsteps, gather=True, with_rw=True)
+        self.run(f, nsteps, gather=True, with_rw=nsteps > 0)
         if out is not None:
             s.fetch(*out)
         else:
