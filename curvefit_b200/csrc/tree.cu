@@ -609,41 +609,50 @@ tree_eval_kernel(const TreeParams prm)
     // ---- phase 3: range ends, element by element (:542-556 per pair)
     {
         // adjacent pieces are merged: [l9,hdL) | [tlL,l1)+[l1,hdC) | [tlC,r1+1)+[r1+1,hdR) | [tlR,r9+1).
-        // Two independent streams per lane -- A: pieces 1, 2 (left of the core), B: pieces 3, 4 --
-        // with their own accumulators: half the trip count and two dependency chains in flight.
-        int32_t ja = l9, ea = hdL, jb = tlC, eb = hdR;
-        bool a2 = false, b2 = false;
-        auto settle_a = [&]() -> bool {
-            if (ja >= ea && !a2) { a2 = true; ja = tlL; ea = hdC; }
-            return ja < ea;
-        };
-        auto settle_b = [&]() -> bool {
-            if (jb >= eb && !b2) { b2 = true; jb = tlR; eb = r9 + 1; }
-            return jb < eb;
-        };
-        bool ha = valid && settle_a(), hb = valid && settle_b();
-        Moments mb = {0.0, 0.0, 0.0, 0.0, 0.0};
-        auto pair = [&](int32_t j, bool on, Moments& acc) {
-            const double q = (x[j] - xs) * invh;
-            const double tt = fma(-(q * q), fabs(q), 1.0);
-            double wgt = (tt * tt) * tt;
-            wgt = (j >= l1 && j <= r1) ? 1.0 : wgt;                 // :547-551
-            wgt = on ? wgt : 0.0;
-            const double wr = rw ? wgt * rw[j] : wgt;
-            const double wq = wr * q;
-            const double yj = y[j];
-            acc.S0 += wr;
-            acc.S1 += wq;
-            acc.S2 = fma(wq, q, acc.S2);
-            acc.T0 = fma(wr, yj, acc.T0);
-            acc.T1 = fma(wq, yj, acc.T1);
-        };
+        // Two independent streams per lane -- A: pieces 1, 2 (left of the core and its head),
+        // B: pieces 3, 4 -- with their own accumulators, walked by ONE counter k: element k of a
+        // stream is j1 + k in its first piece, j2 + (k - c1) in its second.  Inside A an element
+        // belongs to the w = 1 core iff j >= l1, inside B iff j <= r1 (:547-551).
+        const int32_t c1a = valid ? max(hdL - l9, 0) : 0, ca = c1a + (valid ? max(hdC - tlL, 0) : 0);
+        const int32_t c1b = valid ? max(hdR - tlC, 0) : 0, cb = c1b + (valid ? max(r9 + 1 - tlR, 0) : 0);
+        const int32_t d2a = tlL - c1a, d2b = tlR - c1b;           // j = d2 + k in the second piece
         const int32_t safe = valid ? i : 0;
-        while (__any_sync(kFull, ha || hb)) {
-            pair(ha ? ja : safe, ha, m);
-            pair(hb ? jb : safe, hb, mb);
-            if (ha) { ++ja; ha = settle_a(); }
-            if (hb) { ++jb; hb = settle_b(); }
+        Moments mb = {0.0, 0.0, 0.0, 0.0, 0.0};
+        const int32_t kmax = max(ca, cb);
+        for (int32_t k = 0; __any_sync(kFull, k < kmax); ++k) {
+            const bool ona = k < ca, onb = k < cb;
+            const int32_t ja = ona ? (k < c1a ? l9 + k : d2a + k) : safe;
+            const int32_t jb = onb ? (k < c1b ? tlC + k : d2b + k) : safe;
+            {
+                const double q = (x[ja] - xs) * invh;
+                const double tt = fma(-(q * q), fabs(q), 1.0);
+                double wgt = (tt * tt) * tt;
+                wgt = ja >= l1 ? 1.0 : wgt;
+                wgt = ona ? wgt : 0.0;
+                const double wr = rw ? wgt * rw[ja] : wgt;
+                const double wq = wr * q;
+                const double yj = y[ja];
+                m.S0 += wr;
+                m.S1 += wq;
+                m.S2 = fma(wq, q, m.S2);
+                m.T0 = fma(wr, yj, m.T0);
+                m.T1 = fma(wq, yj, m.T1);
+            }
+            {
+                const double q = (x[jb] - xs) * invh;
+                const double tt = fma(-(q * q), fabs(q), 1.0);
+                double wgt = (tt * tt) * tt;
+                wgt = jb <= r1 ? 1.0 : wgt;
+                wgt = onb ? wgt : 0.0;
+                const double wr = rw ? wgt * rw[jb] : wgt;
+                const double wq = wr * q;
+                const double yj = y[jb];
+                mb.S0 += wr;
+                mb.S1 += wq;
+                mb.S2 = fma(wq, q, mb.S2);
+                mb.T0 = fma(wr, yj, mb.T0);
+                mb.T1 = fma(wq, yj, mb.T1);
+            }
         }
         m.S0 += mb.S0; m.S1 += mb.S1; m.S2 += mb.S2; m.T0 += mb.T0; m.T1 += mb.T1;
     }
