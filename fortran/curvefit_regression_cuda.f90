@@ -19,11 +19,17 @@ module curvefit_regression_cuda
     use, intrinsic :: iso_c_binding
     use, intrinsic :: iso_fortran_env, only : int32, real64
     use curvefit_core, only : CF_ARRAY_SIZE_ERROR, CF_OUT_OF_MEMORY_ERROR, &
-        CF_NO_DATA_DEFINED_ERROR
+        CF_NO_DATA_DEFINED_ERROR, CF_INVALID_INPUT_ERROR
     use ferror, only : errors
     implicit none
     private
     public :: lowess_smoothing
+    public :: moving_average
+
+    !> Same generic name as the reference (src/curvefit_regression.f90:82-84).
+    interface moving_average
+        module procedure :: moving_average_1
+    end interface
 
     !> Code libcurvefit_cuda returns for a CUDA failure (no reference equivalent).
     integer(int32), parameter :: CF_DEVICE_ERROR = 303
@@ -67,6 +73,14 @@ module curvefit_regression_cuda
             integer(c_int32_t) :: rc
         end function
 
+        function cf_moving_average(x, n, npts) bind(C, name = "cf_moving_average") &
+                result(rc)
+            import :: c_int32_t, c_double
+            real(c_double), intent(inout) :: x(*)
+            integer(c_int32_t), value :: n, npts
+            integer(c_int32_t) :: rc
+        end function
+
         function cf_last_error(buf, len) bind(C, name = "cf_last_error") result(rc)
             import :: c_int32_t, c_char
             character(kind = c_char), intent(out) :: buf(*)
@@ -100,6 +114,49 @@ contains
             end do
             call errmgr%report_error(fcn, trim(msg), rc)
         end select
+    end subroutine
+
+    ! reference moving_average_1, src/curvefit_regression.f90:427-478 (bit-identical result)
+    subroutine moving_average_1(x, npts, err)
+        real(real64), intent(inout), dimension(:) :: x
+        integer(int32), intent(in) :: npts
+        class(errors), intent(inout), optional, target :: err
+
+        integer(int32) :: i, n, flag, rc
+        real(real64), allocatable, dimension(:) :: xc
+        class(errors), pointer :: errmgr
+        type(errors), target :: deferr
+
+        n = size(x)
+        if (present(err)) then
+            errmgr => err
+        else
+            errmgr => deferr
+        end if
+        if (npts < 2 .or. npts > n) then
+            call errmgr%report_error("moving_average_1", &
+                "The averaging size window must be at least 2, and less " // &
+                "than the size of the data set.", CF_INVALID_INPUT_ERROR)
+            return
+        end if
+        ! x is assumed-shape and may be strided: the C entry point takes a contiguous copy
+        allocate(xc(n), stat = flag)
+        if (flag /= 0) then
+            call errmgr%report_error("moving_average_1", &
+                "Insufficient memory available.", CF_OUT_OF_MEMORY_ERROR)
+            return
+        end if
+        do concurrent (i = 1:n)
+            xc(i) = x(i)
+        end do
+        rc = cf_moving_average(xc, n, npts)
+        if (rc /= 0) then
+            call report(errmgr, "moving_average_1", rc)
+            return
+        end if
+        do concurrent (i = 1:n)
+            x(i) = xc(i)
+        end do
     end subroutine
 
     ! reference ls_init, src/curvefit_regression.f90:740-811
