@@ -387,42 +387,52 @@ tree_chain_kernel(const TreeParams prm, int g)
 
 // The nodes that tile the leaf range [la, lb): per chain level at most one suffix node (left
 // end) and one prefix node (right end), then the binary walk over what is left where both
-// ends share a block.  Yields node indices into TreeParams::nodes.
+// ends share a block.  Yields node indices into TreeParams::nodes (total < n, so 32 bits).
+// Five registers of state: the evaluator's occupancy is bought with them.
 struct Chain {
-    int32_t a, b;
-    int g, stage, cb;
-    bool tail;
-    Walk w;
+    int32_t a, b;   // what is left to tile, in units of the level being climbed
+    int g;          // chain level 1..ngroups while climbing the chains, 0 = binary tail
+    int st;         // chains: 0 test / left end, 1 right end, 2 climb;  tail: 0 / 1 as Walk::sub
+    int lv;         // binary level of a, b in the tail
     __device__ __forceinline__ void start(int32_t la, int32_t lb)
     {
-        a = la; b = lb; g = 1; stage = 0; cb = 0; tail = false;
-        if (a >= b) { a = b = 0; tail = true; w.start(0, 0); }
+        a = la; b = lb; g = 1; st = 0; lv = 0;
+        if (a >= b) { a = b = 0; g = 0; }
     }
-    __device__ __forceinline__ bool next(const TreeParams& prm, int64_t& node)
+    __device__ __forceinline__ bool next(const TreeParams& prm, int32_t& node)
     {
-        while (!tail) {
-            if (stage == 0) {
-                cb = g <= prm.ngroups ? prm.cbits[g] : 0;
+        while (g) {
+            const int cb = g <= prm.ngroups ? prm.cbits[g] : 0;
+            const int32_t cm = (1 << cb) - 1;
+            if (st == 0) {
                 if (cb == 0 || (a >> cb) == ((b - 1) >> cb)) {
-                    tail = true;
-                    w.start_at(a, b, prm.ulev[min(g, prm.ngroups + 1)]);
+                    lv = prm.ulev[g];
+                    g = 0;
                     break;
                 }
-                stage = 1;
-                const int32_t cm = (1 << cb) - 1;
-                if (a & cm) { node = prm.coff[g] + a; a = (a | cm) + 1; return true; }
+                st = 1;
+                if (a & cm) { node = (int32_t)prm.coff[g] + a; a = (a | cm) + 1; return true; }
             }
-            if (stage == 1) {
-                stage = 2;
-                const int32_t cm = (1 << cb) - 1;
-                if (b & cm) { node = prm.coff[g] + prm.cnt[prm.ulev[g]] + (b - 1); b &= ~cm; return true; }
+            if (st == 1) {
+                st = 2;
+                if (b & cm) { node = (int32_t)prm.coff[g] + prm.cnt[prm.ulev[g]] + (b - 1); b &= ~cm; return true; }
             }
-            a >>= cb; b >>= cb; ++g; stage = 0;
-            if (a >= b) { tail = true; w.start(0, 0); return false; }
+            a >>= cb; b >>= cb; ++g; st = 0;
+            if (a >= b) { a = b = 0; g = 0; return false; }
         }
-        int lv;
-        int32_t idx;
-        if (w.next(lv, idx)) { node = prm.off[lv] + idx; return true; }
+        while (a < b) {                                   // as Walk::next
+            if (st == 0) {
+                st = 1;
+                if (a & 1) { node = (int32_t)prm.off[lv] + a; ++a; return true; }
+            }
+            st = 0;
+            const bool t = b & 1;
+            const int32_t id = b - 1;
+            const int l0 = lv;
+            if (t) b = id;
+            a >>= 1; b >>= 1; ++lv;
+            if (t) { node = (int32_t)prm.off[l0] + id; return true; }
+        }
         return false;
     }
 };
@@ -526,44 +536,56 @@ __device__ __forceinline__ void take_core(const double* __restrict__ nd, double 
 //   1. tricube nodes of [lo9, lo1) and (hi1, hi9]   (~110 FP64 instr each)
 //   2. core nodes of [lo1, hi1]                     (~15)
 //   3. the < 16 elements at either end of each range, reference formula (~13 each)
-// (Tried and dropped, B200, n = 1e8: a one-node-ahead prefetch, splitting the phases into
-// two kernels, advancing the left and right walks together -- all within 2 % or slower;
-// occupancy below 5 CTAs of 128 threads per SM costs 10-40 %.)
-template <int NT, int MINB>
+// (Tried and dropped, B200, n = 1e8: loading one node ahead into registers, splitting the
+// phases into two kernels, advancing the left and right walks together -- all within 2 % or
+// slower; occupancy is what pays, see the register diet below.)
+template <int NT, int MINB, int PF>
 __global__ void __launch_bounds__(NT, MINB)
 tree_eval_kernel(const TreeParams prm)
 {
-    const size_t soff = (size_t)blockIdx.y * (size_t)prm.n;
-    const double* __restrict__ x = prm.x + soff;
-    const double* __restrict__ y = prm.y + soff;
-    const double* __restrict__ rw = prm.rw ? prm.rw + soff : nullptr;
+    // Register diet: the kernel waits on node loads, so occupancy is what pays (6 CTAs of
+    // 128 threads per SM instead of 5: -7 %; 7: another -1 %).  Nothing but the moments, xs,
+    // 1/h, the walk and the point's index lives through phase 1: the series offset is
+    // rebuilt from %ctaid.y (soff(), opaque to the compiler so that it is not kept), the
+    // range bounds are re-read from the window arrays at the start of each phase (ldv(),
+    // volatile for the same reason) and the bandwidth h is rebuilt at the end.
+    auto soff = [&]() -> size_t {
+        unsigned s;
+        asm volatile("mov.u32 %0, %%ctaid.y;" : "=r"(s));
+        return (size_t)s * (size_t)prm.n;
+    };
+    auto ldv = [](const int32_t* p) -> int32_t {
+        int32_t v;
+        asm volatile("ld.global.nc.s32 %0, [%1];" : "=r"(v) : "l"(p));
+        return v;
+    };
     const double* __restrict__ nodes = prm.nodes + (size_t)blockIdx.y * prm.total * kNodeLen;
-    const int32_t slot = prm.begin + blockIdx.x * NT + threadIdx.x;
 
     // tie followers copy their leader's value later (robust.cu); a shard that starts
     // inside a tie group fits its first point in the leader's place (as fit.cu)
-    bool valid = slot < prm.end;
-    const int32_t i = (valid && prm.fidx) ? __ldg(prm.fidx + slot) : slot;
-    if (valid && !prm.fidx) {
-        const int32_t l = prm.w.leader[soff + i];
-        valid = (l == i) || (i == prm.begin && l < i);
-    }
-    double xs = 0.0, h = 0.0, invh = 0.0;
-    int32_t l9 = 0, r9 = -1, l1 = 0, r1 = -1;
-    if (valid) {
-        const int32_t nl = prm.w.nleft[soff + i];
-        xs = x[i];
-        const double hl = xs - x[nl], hr = x[nl + prm.ns - 1] - xs;        // :536
-        h = hl > hr ? hl : hr;
-        invh = h > 0.0 ? 1.0 / h : 0.0;
-        l9 = prm.w.lo9[soff + i]; r9 = prm.w.hi9[soff + i];
-        l1 = prm.w.lo1[soff + i]; r1 = prm.w.hi1[soff + i];
+    int32_t i;                                   // the point, -1 = this lane fits nothing
+    double xs = 0.0, invh = 0.0;
+    {
+        const size_t so = soff();
+        const int32_t slot = prm.begin + blockIdx.x * NT + threadIdx.x;
+        bool valid = slot < prm.end;
+        i = (valid && prm.fidx) ? __ldg(prm.fidx + slot) : slot;
+        if (valid && !prm.fidx) {
+            const int32_t l = prm.w.leader[so + i];
+            valid = (l == i) || (i == prm.begin && l < i);
+        }
+        if (valid) {
+            const double* __restrict__ x = prm.x + so;
+            const int32_t nl = prm.w.nleft[so + i];
+            xs = x[i];
+            const double hl = xs - x[nl], hr = x[nl + prm.ns - 1] - xs;    // :536
+            const double h = hl > hr ? hl : hr;
+            invh = h > 0.0 ? 1.0 / h : 0.0;
+        } else {
+            i = -1;
+        }
     }
     // ranges: L = [l9, l1), C = [l1, r1 + 1), R = [r1 + 1, r9 + 1)
-    int32_t hdL, tlL, laL, lbL, hdC, tlC, laC, lbC, hdR, tlR, laR, lbR;
-    split_range(l9, l1, hdL, tlL, laL, lbL);
-    split_range(l1, r1 + 1, hdC, tlC, laC, lbC);
-    split_range(r1 + 1, r9 + 1, hdR, tlR, laR, lbR);
 
     Moments m = {0.0, 0.0, 0.0, 0.0, 0.0};
     constexpr unsigned kFull = 0xffffffffu;
@@ -571,37 +593,74 @@ tree_eval_kernel(const TreeParams prm)
     // ---- phase 1: tricube nodes, left range then right range
     {
         Chain w;
-        w.start(laL, lbL);
+        {
+            int32_t hd, tl, la = 0, lb = 0;
+            if (i >= 0) {
+                const size_t pi = soff() + i;
+                split_range(ldv(prm.w.lo9 + pi), ldv(prm.w.lo1 + pi), hd, tl, la, lb);
+            }
+            w.start(la, lb);
+        }
         int phase = 0;
-        int64_t node = 0;
+        int32_t node = 0;
         double nsig = 1.0;
         auto advance = [&]() -> bool {
             if (w.next(prm, node)) return true;
             if (phase == 0) {
                 phase = 1;
                 nsig = -1.0;
-                w.start(laR, lbR);
+                int32_t hd, tl, la = 0, lb = 0;
+                if (i >= 0) {
+                    const size_t pi = soff() + i;
+                    split_range(ldv(prm.w.hi1 + pi) + 1, ldv(prm.w.hi9 + pi) + 1, hd, tl, la, lb);
+                }
+                w.start(la, lb);
                 return w.next(prm, node);
             }
             return false;
         };
         bool have = advance();
-        while (__any_sync(kFull, have)) {
-            if (have) {
-                take_tricube(nodes + node * kNodeLen, xs, invh, nsig, m);
-                have = advance();
+        if (PF == 0) {
+            while (__any_sync(kFull, have)) {
+                if (have) {
+                    take_tricube(nodes + (size_t)node * kNodeLen, xs, invh, nsig, m);
+                    have = advance();
+                }
+            }
+        } else {
+            // the index of the node after this one is known before this one is evaluated:
+            // ask for its two lines while the ~110 FP64 instructions of this one run
+            while (__any_sync(kFull, have)) {
+                if (have) {
+                    const double* cur = nodes + (size_t)node * kNodeLen;
+                    const double sg = nsig;
+                    have = advance();
+                    if (have) {
+                        const double* nx = nodes + (size_t)node * kNodeLen;
+                        asm volatile("prefetch.global.L1 [%0];" :: "l"(nx));
+                        asm volatile("prefetch.global.L1 [%0];" :: "l"(nx + 16));
+                    }
+                    take_tricube(cur, xs, invh, sg, m);
+                }
             }
         }
     }
     // ---- phase 2: core nodes
     {
         Chain w;
-        w.start(laC, lbC);
-        int64_t node = 0;
+        {
+            int32_t hd, tl, la = 0, lb = 0;
+            if (i >= 0) {
+                const size_t pi = soff() + i;
+                split_range(ldv(prm.w.lo1 + pi), ldv(prm.w.hi1 + pi) + 1, hd, tl, la, lb);
+            }
+            w.start(la, lb);
+        }
+        int32_t node = 0;
         bool have = w.next(prm, node);
         while (__any_sync(kFull, have)) {
             if (have) {
-                take_core(nodes + node * kNodeLen, xs, invh, m);
+                take_core(nodes + (size_t)node * kNodeLen, xs, invh, m);
                 have = w.next(prm, node);
             }
         }
@@ -613,6 +672,21 @@ tree_eval_kernel(const TreeParams prm)
         // B: pieces 3, 4 -- with their own accumulators, walked by ONE counter k: element k of a
         // stream is j1 + k in its first piece, j2 + (k - c1) in its second.  Inside A an element
         // belongs to the w = 1 core iff j >= l1, inside B iff j <= r1 (:547-551).
+        const bool valid = i >= 0;
+        const size_t so = soff();
+        const double* __restrict__ x = prm.x + so;
+        const double* __restrict__ y = prm.y + so;
+        const double* __restrict__ rw = prm.rw ? prm.rw + so : nullptr;
+        int32_t l9 = 0, r9 = -1, l1 = 0, r1 = -1;
+        if (valid) {
+            const size_t pi = so + i;
+            l9 = ldv(prm.w.lo9 + pi); r9 = ldv(prm.w.hi9 + pi);
+            l1 = ldv(prm.w.lo1 + pi); r1 = ldv(prm.w.hi1 + pi);
+        }
+        int32_t hdL, tlL, hdC, tlC, hdR, tlR, la, lb;
+        split_range(l9, l1, hdL, tlL, la, lb);
+        split_range(l1, r1 + 1, hdC, tlC, la, lb);
+        split_range(r1 + 1, r9 + 1, hdR, tlR, la, lb);
         const int32_t c1a = valid ? max(hdL - l9, 0) : 0, ca = c1a + (valid ? max(hdC - tlL, 0) : 0);
         const int32_t c1b = valid ? max(hdR - tlC, 0) : 0, cb = c1b + (valid ? max(r9 + 1 - tlR, 0) : 0);
         const int32_t d2a = tlL - c1a, d2b = tlR - c1b;           // j = d2 + k in the second piece
@@ -656,9 +730,15 @@ tree_eval_kernel(const TreeParams prm)
         }
         m.S0 += mb.S0; m.S1 += mb.S1; m.S2 += mb.S2; m.T0 += mb.T0; m.T1 += mb.T1;
     }
-    if (valid) {
+    if (i >= 0) {
+        const size_t so = soff();
+        const double* __restrict__ x = prm.x + so;
+        const int32_t nl = ldv(prm.w.nleft + so + i);
+        const double hl = xs - x[nl], hr = x[nl + prm.ns - 1] - xs;        // :536, as above
+        const double h = hl > hr ? hl : hr;
         const double range = x[prm.n - 1] - x[0];                          // :535
-        prm.ys[soff + i] = fit_value(m.S0, m.S1, m.S2, m.T0, m.T1, y[i], h, h, 0.0, range);
+        const double y = prm.y[so + i];
+        prm.ys[so + i] = fit_value(m.S0, m.S1, m.S2, m.T0, m.T1, y, h, h, 0.0, range);
     }
 }
 
@@ -760,7 +840,17 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
         h->launches++;
     }
     const int cntp = prm.end - prm.begin;
-    tree_eval_kernel<128, 5><<<dim3((cntp + 127) / 128, h->nseries), 128, 0, h->stream>>>(prm);
+    // 7 CTAs of 128 threads per SM (72 registers) + L1 prefetch of the next node; the
+    // others are kept for measurement (B200, n = 1e8 smooth: 5 CTAs 143.2 ms, 6: 128.6,
+    // 7: 125.7, 7 + prefetch 125.3)
+    static const int variant = getenv("CF_TREE_EVAL") ? atoi(getenv("CF_TREE_EVAL")) : 7;
+    const dim3 eg((cntp + 127) / 128, h->nseries);
+    switch (variant) {
+    case 5:  tree_eval_kernel<128, 5, 0><<<eg, 128, 0, h->stream>>>(prm); break;
+    case 6:  tree_eval_kernel<128, 6, 0><<<eg, 128, 0, h->stream>>>(prm); break;
+    case 70: tree_eval_kernel<128, 7, 0><<<eg, 128, 0, h->stream>>>(prm); break;
+    default: tree_eval_kernel<128, 7, 1><<<eg, 128, 0, h->stream>>>(prm); break;
+    }
     CF_CUDA(cudaGetLastError());
     h->launches++;
     h->fit_launches++;

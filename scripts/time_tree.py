@@ -1,5 +1,5 @@
 """Times both evaluators (direct kernel / moment tree) on one resident series.
-    python scripts/time_tree.py n f nsteps [direct_too] [delta]"""
+    python scripts/time_tree.py n f nsteps [direct_too] [delta]      (CF_TT_X=random: sorted random x)"""
 import sys, os
 sys.path.insert(0, os.path.join(os.path.dirname(__file__), ".."))
 import numpy as np
@@ -8,7 +8,8 @@ from curvefit_b200 import datagen, lowess_smoothing
 n = int(float(sys.argv[1])); f = float(sys.argv[2]); nsteps = int(sys.argv[3])
 both = len(sys.argv) > 4 and sys.argv[4] == "1"
 delta = float(sys.argv[5]) if len(sys.argv) > 5 else 0.0
-x = datagen.grid_x(n); y = datagen.noisy_y(x)
+x = np.sort(datagen.random_x(n)) if os.environ.get("CF_TT_X") == "random" else datagen.grid_x(n)
+y = datagen.noisy_y(x)
 res = {}
 for m in (["direct"] if both else []) + ["tree"]:
     fit = lowess_smoothing(); fit.set_method(m); fit.initialize(x, y, srt=False)
