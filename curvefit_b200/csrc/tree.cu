@@ -97,20 +97,17 @@ __device__ __forceinline__ bool node_needed(const TreeParams& prm, int series, i
 }
 
 // ---- build: leaves -------------------------------------------------------------------
-__global__ void __launch_bounds__(128)
-tree_leaf_kernel(const TreeParams prm)
+__device__ __forceinline__ void build_leaf(const TreeParams& prm, int series, int32_t leaf)
 {
-    const int32_t leaf = blockIdx.x * blockDim.x + threadIdx.x;
-    if (leaf >= prm.cnt[0]) return;
-    const size_t soff = (size_t)blockIdx.y * (size_t)prm.n;
+    const size_t soff = (size_t)series * (size_t)prm.n;
     const double* __restrict__ x = prm.x + soff;
     const double* __restrict__ y = prm.y + soff;
     const double* __restrict__ rw = prm.rw ? prm.rw + soff : nullptr;
-    double* __restrict__ nd = prm.nodes + ((size_t)blockIdx.y * prm.total + leaf) * kNodeLen;
+    double* __restrict__ nd = prm.nodes + ((size_t)series * prm.total + leaf) * kNodeLen;
 
     int32_t j0, j1;
     node_span(0, leaf, prm.n, j0, j1);
-    if (!node_needed(prm, blockIdx.y, j0, j1)) return;
+    if (!node_needed(prm, series, j0, j1)) return;
     const double xf = x[j0], xl = x[j1];
     const double c = 0.5 * xf + 0.5 * xl;
     const double d = 0.5 * (xl - xf);
@@ -139,6 +136,13 @@ tree_leaf_kernel(const TreeParams prm)
 #pragma unroll
     for (int k = 0; k < 5; ++k) o[7 + k] = make_double2(Bm[2 * k], Bm[2 * k + 1]);
     o[12] = make_double2(Bm[10], 0.0);
+}
+
+__global__ void __launch_bounds__(128)
+tree_leaf_kernel(const TreeParams prm)
+{
+    const int32_t leaf = blockIdx.x * blockDim.x + threadIdx.x;
+    if (leaf < prm.cnt[0]) build_leaf(prm, blockIdx.y, leaf);
 }
 
 // ---- build: parents ------------------------------------------------------------------
@@ -233,6 +237,11 @@ __device__ __forceinline__ void node_load(const double* nd, NodeRegs& r)
     for (int k = 0; k < kKA; ++k) r.A[k] = nd[2 + k];
 #pragma unroll
     for (int k = 0; k < kKB; ++k) r.B[k] = nd[2 + kKA + k];
+}
+__device__ __forceinline__ void node_prefetch(const double* nd)
+{
+    asm volatile("prefetch.global.L1 [%0];" :: "l"(nd));
+    asm volatile("prefetch.global.L1 [%0];" :: "l"(nd + 16));
 }
 __device__ __forceinline__ void node_store(double* nd, const NodeRegs& r)
 {
@@ -332,19 +341,12 @@ tree_chain_entry_kernel(const TreeParams prm, int g)
 // swept left to right, one merge and one stored node per unit; SUF mirrors it.
 constexpr int kChainSeg = 16;
 
-__global__ void __launch_bounds__(128)
-tree_chain_kernel(const TreeParams prm, int g)
+__device__ __forceinline__ void chain_segment(const TreeParams& prm, int g, int series, int32_t seg,
+                                              int32_t sg, int dir)
 {
     const int ulev = prm.ulev[g];
     const int32_t cm = (1 << prm.cbits[g]) - 1;
     const int32_t ucnt = prm.cnt[ulev];
-    const int32_t seg = min(kChainSeg, cm + 1);                              // never across blocks
-    const int32_t nseg = (ucnt + seg - 1) / seg;
-    const int32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
-    const int32_t sg = tid >> 1;
-    const int dir = tid & 1;
-    if (sg >= nseg) return;
-    const int series = blockIdx.y;
     const int32_t s0 = sg * seg, s1 = min(s0 + seg, ucnt);                  // units [s0, s1)
     const int32_t t0 = s0 & ~cm, t1 = min(t0 + cm + 1, ucnt);               // their block
     {   // only what the windows of this shard can reach
@@ -373,15 +375,77 @@ tree_chain_kernel(const TreeParams prm, int g)
     if (dir == 0) {
         for (int32_t t = s0; t < s1; ++t) {
             node_load(units + (size_t)t * kNodeLen, u);
+            if (t + 1 < s1) node_prefetch(units + (size_t)(t + 1) * kNodeLen);
             if (have) { node_merge(acc, u, nx); acc = nx; } else { acc = u; have = true; }
             node_store(pre + (size_t)t * kNodeLen, acc);
         }
     } else {
         for (int32_t t = s1 - 1; t >= s0; --t) {
             node_load(units + (size_t)t * kNodeLen, u);
+            if (t > s0) node_prefetch(units + (size_t)(t - 1) * kNodeLen);
             if (have) { node_merge(acc, u, nx); acc = nx; } else { acc = u; have = true; }
             node_store(suf + (size_t)t * kNodeLen, acc);
         }
+    }
+}
+
+__global__ void __launch_bounds__(128)
+tree_chain_kernel(const TreeParams prm, int g)
+{
+    const int32_t seg = min(kChainSeg, 1 << prm.cbits[g]);                   // never across blocks
+    const int32_t nseg = (prm.cnt[prm.ulev[g]] + seg - 1) / seg;
+    const int32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+    if ((tid >> 1) < nseg) chain_segment(prm, g, blockIdx.y, seg, tid >> 1, tid & 1);
+}
+
+// ---- build: one launch per block of leaves ------------------------------------------------
+// One CTA per block of 2^cb leaves builds everything that lives inside the block: its
+// leaves, the binary levels 1 .. cb above them and (chain != 0) the level-1 chain PRE_1 /
+// SUF_1, phase after phase with the block's nodes still in L2 -- the separate kernels
+// re-read each level from HBM (leaf + merges + chain: 15.2 GB per pass at n = 1e8, fused:
+// 8.8 GB, of which 6.4 GB are the stores).
+// What it buys is launches, not bandwidth: at n = 1e6 a smooth drops from 2.35 to 1.71 ms
+// (79 -> 59 launches), at n = 1e8 the build stays at ~5.3 ms per pass.  ncu there: l1tex
+// throughput 87 %, DRAM 23 % -- a node per thread is 25 loads / 13 stores at a stride of
+// 256 B between lanes, 32 lines per warp instruction.  Moving the nodes through a per-warp
+// shared-memory stage (the warp fetching lane i's node with 25 lanes at once) was measured
+// and dropped: staging loads and stores 147 ms per smooth instead of 120 (the 32-step
+// fetch loop serialises the load latency), staging only the stores and the leaf inputs
+// 120.0-123.3 ms, no gain.
+// NT = 32: one warp per block, __syncwarp between the phases -- no warp waits at a barrier
+// for the few lanes that build the upper levels, and 16 such CTAs fit an SM; best for many
+// blocks.  NT = 128: shortest critical path per block; best when the blocks are few.
+template <int NT>
+__global__ void __launch_bounds__(NT, 512 / NT)
+tree_block_kernel(const TreeParams prm, int cb, int chain, int seg)
+{
+    const int series = blockIdx.y;
+    const int32_t blk0 = blockIdx.x << cb;
+    const int32_t blk1 = min(blk0 + (1 << cb), prm.cnt[0]);
+    {   // a block none of whose elements the shard's windows reach has nothing to build
+        const int32_t lo = __ldg(prm.span + 2 * series), hi = __ldg(prm.span + 2 * series + 1);
+        int32_t e0, e1, k0, k1;
+        node_span(0, blk0, prm.n, e0, k0);
+        node_span(0, blk1 - 1, prm.n, k1, e1);
+        if (e1 < lo || e0 > hi) return;
+    }
+    auto sync = [] {
+        __threadfence_block();
+        if (NT == 32) __syncwarp(); else __syncthreads();
+    };
+    for (int32_t leaf = blk0 + threadIdx.x; leaf < blk1; leaf += NT) build_leaf(prm, series, leaf);
+    sync();
+    const double* __restrict__ x = prm.x + (size_t)series * (size_t)prm.n;
+    double* base = prm.nodes + (size_t)series * prm.total * kNodeLen;
+    for (int level = 1; level <= cb && level < prm.nlevels; ++level) {
+        const int32_t k0 = blk0 >> level, k1 = ((blk1 - 1) >> level) + 1;
+        for (int32_t k = k0 + threadIdx.x; k < k1; k += NT) build_parent(prm, x, base, level, k, series);
+        sync();
+    }
+    if (chain) {
+        const int32_t sg0 = blk0 / seg, sg1 = (blk1 - 1) / seg + 1;
+        for (int32_t task = threadIdx.x; task < 2 * (sg1 - sg0); task += NT)
+            chain_segment(prm, 1, series, seg, sg0 + (task >> 1), task & 1);
     }
 }
 
@@ -814,10 +878,33 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
     prm.nodes = h->tree;
     prm.span = h->span;
 
-    tree_leaf_kernel<<<dim3((prm.cnt[0] + 127) / 128, h->nseries), 128, 0, h->stream>>>(prm);
-    CF_CUDA(cudaGetLastError());
-    h->launches++;
+    // the part of the tree inside each block of 2^cb leaves in one launch (with the level-1
+    // chain when its blocks are those); CF_TREE_FUSED=0: one launch per level as before
+    static const bool fused = !(getenv("CF_TREE_FUSED") && atoi(getenv("CF_TREE_FUSED")) == 0);
     int level = 1;
+    int g0 = 1;
+    if (fused) {
+        const bool chain = prm.ngroups >= 1;
+        int cb = chain ? prm.cbits[1] : 8;
+        if (cb > L - 1) cb = L - 1;
+        // few blocks: 128 threads per block (shortest critical path); many: one warp per block
+        static const int bt_env = getenv("CF_TREE_BLOCK") ? atoi(getenv("CF_TREE_BLOCK")) : 0;
+        const int64_t leaves = (int64_t)prm.cnt[0] * h->nseries;
+        const int bt = bt_env ? bt_env : (leaves < (1 << 20) ? 128 : 32);
+        const dim3 bg((prm.cnt[0] + (1 << cb) - 1) >> cb, h->nseries);
+        int seg = bt == 128 ? 8 : 16;                            // units per chain task
+        if (seg > (1 << cb)) seg = 1 << cb;
+        if (bt == 128) tree_block_kernel<128><<<bg, 128, 0, h->stream>>>(prm, cb, chain, seg);
+        else           tree_block_kernel<32><<<bg, 32, 0, h->stream>>>(prm, cb, chain, seg);
+        CF_CUDA(cudaGetLastError());
+        h->launches++;
+        level = cb + 1;
+        if (chain) g0 = 2;
+    } else {
+        tree_leaf_kernel<<<dim3((prm.cnt[0] + 127) / 128, h->nseries), 128, 0, h->stream>>>(prm);
+        CF_CUDA(cudaGetLastError());
+        h->launches++;
+    }
     for (; level < L && prm.cnt[level] > 2048; ++level) {
         tree_merge_kernel<<<dim3((prm.cnt[level] + 127) / 128, h->nseries), 128, 0, h->stream>>>(prm, level);
         CF_CUDA(cudaGetLastError());
@@ -828,7 +915,7 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
         CF_CUDA(cudaGetLastError());
         h->launches++;
     }
-    for (int g = 1; g <= prm.ngroups; ++g) {
+    for (int g = g0; g <= prm.ngroups; ++g) {
         const int32_t ucnt = prm.cnt[prm.ulev[g]];
         const int32_t seg = (1 << prm.cbits[g]) < kChainSeg ? (1 << prm.cbits[g]) : kChainSeg;
         const int32_t nseg = (ucnt + seg - 1) / seg;
