@@ -291,10 +291,10 @@ def run_ours(args):
         if world == 1 and fit_launches and args.method != "direct":
             line["roofline"] = {
                 "bound": "fp64", "achieved": None, "peak": peak_tf, "unit": "TFLOP/s", "frac": None,
-                "traffic": None, "kernel": "cf::tree_eval_kernel",
+                "traffic": None, "kernel": "fit stage = per-pass tree rebuild (cf::tree_block_kernel ...) + cf::tree_eval_kernel",
                 "avg_launch_ms": fit_ms / fit_launches, "share_of_step": fit_ms / total_ms,
                 "note": "moment-tree evaluator: O(n log ns) work, no 17 flop/pair accounting applies; "
-                        "ncu: profiles/r01_tree_eval_c4_ncu_full.csv (FP64 pipe 48% active). The roofline "
+                        "ncu: profiles/r01_tree_eval_c4_ncu_full.csv (FP64 pipe 52% active, l1tex 73%). The roofline "
                         "claim of this repo is the direct kernel's (default --method direct)."}
         elif world == 1 and fit_launches:
             avg_ms = fit_ms / fit_launches
