@@ -555,7 +555,8 @@ def run_batched(args):
         }
         line["config"]["method"] = args.method
         if args.method != "direct":
-            line["roofline"].update({"achieved": None, "frac": None, "kernel": "cf::tree_eval_kernel",
+            line["roofline"].update({"achieved": None, "frac": None,
+                                     "kernel": "fit stage = per-pass tree rebuild (cf::tree_block_kernel ...) + cf::tree_eval_kernel",
                                      "note": "moment-tree evaluator: the 17 flop/pair accounting does not apply"})
         if world == 1 and not args.no_e2e:
             k = min(mine, 512)
