@@ -128,3 +128,45 @@ def test_moving_average_and_median_host_checks_need_no_device():
         assert lib.cf_lowess_smooth_delta(x.ctypes.data_as(_lib.c_dp), x.ctypes.data_as(_lib.c_dp), 6, 0.5, 2, 0.1,
                                           out.ctypes.data_as(_lib.c_dp), out.ctypes.data_as(_lib.c_dp),
                                           out.ctypes.data_as(_lib.c_dp)) == core.CF_DEVICE_ERROR
+
+
+# ---- the boundary from a compiled language (the reference is compiled code) ---------------
+def _cc(args, **kw):
+    import subprocess
+    return subprocess.run(args, cwd=ROOT, capture_output=True, text=True, **kw)
+
+
+@pytest.mark.parametrize("compiler,std", [("gcc", "-std=c99"), ("g++", "-std=c++17")])
+def test_header_is_plain_c_and_cxx(compiler, std, tmp_path):
+    """include/curvefit_cuda.h: no torch / C++ types, compiles pedantically as C99 and as C++."""
+    src = tmp_path / ("t.c" if compiler == "gcc" else "t.cpp")
+    src.write_text('#include "curvefit_cuda.h"\nint main(void) { return cf_version() > 0 ? 0 : 1; }\n')
+    r = _cc([compiler, std, "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only",
+             "-I", os.path.join(ROOT, "include"), str(src)])
+    assert r.returncode == 0, r.stderr
+
+
+def _build_example(tmp_path):
+    exe = str(tmp_path / "lowess_c_abi")
+    libdir = os.path.join(ROOT, "curvefit_b200")
+    r = _cc(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-Iinclude",
+             "examples/lowess_c_abi.c", "-L" + libdir, "-lcurvefit_cuda", "-Wl,-rpath," + libdir,
+             "-lm", "-o", exe])
+    assert r.returncode == 0, r.stderr
+    return exe
+
+
+@pytest.mark.skipif(_have_gpu(), reason="checks the no-GPU failure mode")
+def test_c_example_links_and_fails_loudly_without_a_device(tmp_path):
+    _lib.load()                                   # ImportError if the library has not been built
+    r = _cc([_build_example(tmp_path)], timeout=120)
+    assert r.returncode == 3, (r.returncode, r.stdout, r.stderr)
+    assert "code 303" in r.stderr and "no CPU fallback" in r.stderr
+
+
+@pytest.mark.gpu
+def test_c_example_runs_on_the_device(tmp_path):
+    _lib.load()
+    r = _cc([_build_example(tmp_path)], timeout=300)
+    assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
+    assert "ys =" in r.stdout
