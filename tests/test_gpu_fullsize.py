@@ -140,3 +140,50 @@ def test_c3_full_batched(cf, oracle):
         ok, d, nref = cases.close_or_exact(ys[k], ref["ys"], x[k], y[k], rw[k], f, TOL)
         assert ok, (k, d, nref)
         assert np.max(np.abs(rw[k] - ref["rw"])) < 1e-9, k
+
+
+@pytest.mark.parametrize("kind", ["uniform", "clustered", "ties", "wide"])
+def test_windows_guided_searches_large_irregular(cf, kind):
+    """windows.cu finds every index as "the first j of [lo, hi] where a monotone predicate
+    holds" from a GUESS (carried from the thread's previous point when n is large enough for
+    several points per thread -- here 4).  The defining property is checked for EVERY point
+    with the reference's own floating-point expressions (numpy float64: IEEE, no FMA):
+    the predicate holds at the answer (or the answer is the interval's assumed end) and
+    fails just before it (or the answer is the interval's start).  For a monotone predicate
+    that pins the index uniquely, so this is a bit-exact check at a size the oracle's
+    O(n ns) sweep cannot reach.  (:664-666 slide predicate, :542-556 r <= h9 / r <= h1.)"""
+    n, f = 2_500_000, 0.05
+    x = cases.make_x(kind, n, 7)
+    y = datagen.noisy_y(x)
+    fit = cf.lowess_smoothing()
+    fit.initialize(x, y, srt=False)
+    w = fit.windows(f)
+    from curvefit_b200 import _lib
+    ns = int(_lib.load().cf_lowess_span(n, f))                        # :647
+    assert ns == max(min(int(f * n), n), 2)
+    i = w["leader"].astype(np.int64) - 1
+    assert np.all(x[i] == x) and np.all(i <= np.arange(n))
+    assert np.all((i == 0) | (x[np.maximum(i - 1, 0)] < x[i]))          # first of its tie group
+    xs = x[i]
+    nl = w["nleft"].astype(np.int64) - 1
+    nr = w["nright"].astype(np.int64) - 1
+    l9, r9 = w["lo9"].astype(np.int64) - 1, w["hi9"].astype(np.int64) - 1
+    l1, r1 = w["lo1"].astype(np.int64) - 1, w["hi1"].astype(np.int64) - 1
+    assert np.array_equal(nr, nl + ns - 1) and nl.min() >= 0 and nl.max() <= n - ns
+
+    def slide(L):                                  # x(i) - x(L) <= x(L + ns) - x(i), L + ns < n
+        Lc = np.clip(L, 0, n - ns - 1)
+        return (xs - x[Lc]) <= (x[Lc + ns] - xs)
+    assert np.all((nl == n - ns) | slide(nl))
+    assert np.all((nl == 0) | ~slide(nl - 1))
+
+    h = np.maximum(xs - x[nl], x[nr] - xs)
+    h9, h1 = 0.999 * h, 0.001 * h
+
+    def inside(j, hh):
+        return np.abs(x[np.clip(j, 0, n - 1)] - xs) <= hh
+    assert np.all((nl <= l9) & (l9 <= l1) & (l1 <= i) & (i <= r1) & (r1 <= r9) & (r9 <= n - 1))
+    assert np.all((l9 == i) | inside(l9, h9)) and np.all((l9 == nl) | ~inside(l9 - 1, h9))
+    assert np.all((r9 == i) | inside(r9, h9)) and np.all((r9 == n - 1) | ~inside(r9 + 1, h9))
+    assert np.all((l1 == i) | inside(l1, h1)) and np.all((l1 == l9) | ~inside(l1 - 1, h1))
+    assert np.all((r1 == i) | inside(r1, h1)) and np.all((r1 == r9) | ~inside(r1 + 1, h1))
