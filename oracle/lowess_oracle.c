@@ -11,7 +11,13 @@
  * unseeded noise) and cannot be compiled in this image (no Fortran compiler of
  * any kind).  This file is therefore a line-by-line restatement of the
  * reference's arithmetic, cross-checked against an independent pure-Python
- * transliteration (tests/py_lowess.py) and analytic properties only.
+ * transliteration (tests/py_lowess.py) and analytic properties.  The one
+ * EXTERNAL known answer it is held to is the worked example in the header of
+ * netlib's lowess.f -- the routine the reference's lowess/lowest port
+ * (src/curvefit_regression.f90:508-512, :620-624 cite the same paper): twenty
+ * points, ten tied, F = .25, (NSTEPS, DELTA) = (0, 0), (0, 3), (2, 0), reproduced
+ * to the three printed decimals (tests/cases.NETLIB_*, tests/test_oracle.py).
+ * That anchors the algorithm, not the reference's build of it: still unpinned.
  *
  * Every function cites the reference lines it follows.  Paths are relative to
  * /root/reference; LINALG = src/external/nonlin/src/external/linalg.

@@ -3,7 +3,7 @@
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
 ``--impl reference`` legs may import this module.  The product package
 (curvefit_b200) must never import it.  PARITY UNPINNED: see the header of
-oracle/lowess_oracle.c.
+oracle/lowess_oracle.c (external anchor: the netlib lowess.f worked example).
 """
 from __future__ import annotations
 

@@ -67,3 +67,20 @@ def close_or_exact(got, ref, x, y, rw, f, tol=1e-10, max_referee=64, idx=None):
         if not abs(got[i] - ex) <= tol * max(abs(ex), 1e-3 * scale):
             return False, float(abs(got[i] - ex)), int(bad.size)
     return True, float(d.max(initial=0.0)), int(bad.size)
+
+
+# The worked example printed in the header of netlib's lowess.f (W. S. Cleveland, Bell
+# Laboratories; "go/lowess.f"), the routine the reference's lowess / lowest are a Fortran 90
+# port of (src/curvefit_regression.f90:508-512, :620-624 cite the same paper): twenty points,
+# ten of them with equal abscissas, F = .25, and the smoothed values to three decimals for
+# (NSTEPS, DELTA) = (0, 0), (0, 3), (2, 0).  A published known answer for the ALGORITHM --
+# ties, the delta interpolation and the robustness iterations included; the reference itself
+# holds no LOWESS fixture.
+NETLIB_X = np.array([1, 2, 3, 4, 5] + [6] * 10 + [8, 10, 12, 14, 50], dtype=np.float64)
+NETLIB_Y = np.array([18, 2, 15, 6, 10, 4, 16, 11, 7, 3, 14, 17, 20, 12, 9, 13, 1, 8, 5, 19], dtype=np.float64)
+NETLIB_F = 0.25
+NETLIB_YS = {
+    (0, 0.0): [13.659, 11.145, 8.701, 9.722, 10.000] + [11.300] * 10 + [13.000, 6.440, 5.596, 5.456, 18.998],
+    (0, 3.0): [13.659, 12.347, 11.034, 9.722, 10.511] + [11.300] * 10 + [13.000, 6.440, 5.596, 5.456, 18.998],
+    (2, 0.0): [14.811, 12.115, 8.984, 9.676, 10.000] + [11.346] * 10 + [13.000, 6.734, 5.744, 5.415, 18.998],
+}

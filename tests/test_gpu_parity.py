@@ -261,3 +261,29 @@ def test_large_series_teacher_forced_samples(cf, oracle):
     t = oracle.lowest_at(x, y, f, idx, rw_in)
     ok, d, nref = cases.close_or_exact(ys_next[idx], t["ys"], x, y, rw_in, f, TOL, idx=idx)
     assert ok, (d, nref)
+
+
+@pytest.mark.parametrize("method", ["direct", "tree"])
+@pytest.mark.parametrize("nsteps,delta", sorted(cases.NETLIB_YS))
+def test_published_netlib_example_through_the_c_abi(cf, oracle, method, nsteps, delta):
+    """The worked example in the header of netlib's lowess.f (tests/cases.NETLIB_*: ten tied
+    abscissas, delta interpolation, robustness iterations): both evaluators print the
+    published three decimals and agree with the oracle to 1e-10."""
+    x, y, f = cases.NETLIB_X, cases.NETLIB_Y, cases.NETLIB_F
+    want = np.array(cases.NETLIB_YS[(nsteps, delta)])
+    fit = cf.lowess_smoothing()
+    fit.set_method(method)
+    fit.initialize(x, y, srt=False)
+    if delta > 0.0:
+        fit.set_delta(delta)
+    ys = fit.smooth(f, nsteps=nsteps)
+    assert np.array_equal(np.round(ys, 3), want), np.round(ys, 3) - want
+    ref = oracle.lowess(x, y, f, nsteps, delta)
+    assert cases.close(ys, ref["ys"], 1e-10)[0]
+    # the stateless host-buffer entry points the Fortran shim binds
+    if delta > 0.0:
+        ys2, _, res2 = cf.cf_lowess_smooth_delta(x, y, f, nsteps, delta)
+    else:
+        ys2, _, res2 = cf.cf_lowess_smooth(x, y, f, nsteps)
+    assert np.array_equal(np.round(ys2, 3), want)
+    assert np.array_equal(res2, y - ys2)

@@ -210,3 +210,13 @@ def test_moving_average_oracle_against_python_transliteration(oracle):
         assert rc == 0 and np.array_equal(got, np.array(want))
     assert oracle.moving_average(np.zeros(5), 1)[1] == 201
     assert oracle.moving_average(np.zeros(5), 6)[1] == 201
+
+
+@pytest.mark.parametrize("nsteps,delta", sorted(cases.NETLIB_YS))
+def test_oracle_reproduces_the_published_netlib_example(oracle, nsteps, delta):
+    """Known-answer test of the algorithm the reference ports (tests/cases.NETLIB_*): the
+    oracle must print the same three decimals as the header of netlib's lowess.f."""
+    r = oracle.lowess(cases.NETLIB_X, cases.NETLIB_Y, cases.NETLIB_F, nsteps, delta)
+    want = np.array(cases.NETLIB_YS[(nsteps, delta)])
+    assert np.array_equal(np.round(r["ys"], 3), want), np.round(r["ys"], 3) - want
+    assert np.array_equal(r["res"], cases.NETLIB_Y - r["ys"])
