@@ -220,3 +220,9 @@ def test_oracle_reproduces_the_published_netlib_example(oracle, nsteps, delta):
     want = np.array(cases.NETLIB_YS[(nsteps, delta)])
     assert np.array_equal(np.round(r["ys"], 3), want), np.round(r["ys"], 3) - want
     assert np.array_equal(r["res"], cases.NETLIB_Y - r["ys"])
+
+
+@pytest.mark.parametrize("nsteps,delta", sorted(cases.NETLIB_YS))
+def test_python_transliteration_reproduces_the_published_netlib_example(nsteps, delta):
+    ys = py_lowess.lowess(cases.NETLIB_X, cases.NETLIB_Y, cases.NETLIB_F, nsteps, delta)[0]
+    assert np.array_equal(np.round(np.asarray(ys, dtype=np.float64), 3), np.array(cases.NETLIB_YS[(nsteps, delta)]))
