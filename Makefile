@@ -5,13 +5,18 @@ NVCC     ?= nvcc
 ARCH     := -gencode arch=compute_100a,code=sm_100a
 NVFLAGS  := $(ARCH) -O3 -lineinfo -std=c++17 -Iinclude -Xcompiler -fPIC,-fvisibility=hidden \
             -Xptxas -v -ccbin /usr/bin/g++
+# `make DEV=1`: the development switches (CF_FIT_VARIANT, CF_TREE_BITS, ... read by the sweep
+# scripts under scripts/) are compiled in; a release build has no environment routes.
+ifdef DEV
+NVFLAGS  += -DCF_DEVELOPMENT
+endif
 SRC      := $(wildcard curvefit_b200/csrc/*.cu)
 OBJ      := $(patsubst curvefit_b200/csrc/%.cu,build/%.o,$(SRC))
 LIB      := curvefit_b200/libcurvefit_cuda.so
 
 all: $(LIB)
 
-build/%.o: curvefit_b200/csrc/%.cu curvefit_b200/csrc/common.cuh include/curvefit_cuda.h
+build/%.o: curvefit_b200/csrc/%.cu curvefit_b200/csrc/common.cuh curvefit_b200/csrc/peer.cuh include/curvefit_cuda.h
 	@mkdir -p build
 	$(NVCC) $(NVFLAGS) -c $< -o $@
 

@@ -1,22 +1,28 @@
 #!/usr/bin/env python
 """bench.py -- LOWESS fitted points/sec on B200 (BASELINE.json metric).
 
-A step = one complete smooth() (windows + nsteps+1 fit passes + nsteps
-robustness updates) of the workload.  Default workload = BASELINE.json
-configs[1]: single series n = 1e6, f = 0.05, 3 robustness iterations -- the
-largest configuration that finishes a step in well under a minute on one GPU
-(the headline n = 1e8 needs >= 15 min per step at 100 % of the FP64 roofline;
-run it with --workload c4).
+A step = one complete smooth() (windows + nsteps+1 fit passes + nsteps robustness
+updates) of the workload, inputs resident in HBM.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
     torchrun ... bench.py --gpus N ...        (one rank per GPU, N > 1)
 
-value  : whole-job points/sec, data resident in HBM, CUDA-event timed, max over ranks
-e2e    : the same through the host-buffer C ABI cf_lowess_smooth (pinned host
-         arrays in, host arrays out; copies inside the timed region)
-roofline: the fit kernel against the MEASURED FP64 FMA peak of this GPU
-cpu_baseline / --impl reference: the oracle (C restatement of the reference; the
-         Fortran reference itself cannot be compiled in this image) on the host cores
+The default invocation prints ONE JSON line that carries, at every N:
+
+  value / roofline / e2e   BASELINE configs[1] (n = 1e6, f = 0.05, nsteps = 3) on the DIRECT
+                           kernel -- the O(n ns) sweep the FP64 roofline claim is made on
+  headline_n1e8            the configuration BASELINE.json's metric is quoted on (n = 1e8,
+                           f = 0.05, nsteps = 3, range-sharded over the N ranks) on the
+                           moment-tree evaluator: value, ms_per_step, per-stage ms (max over
+                           ranks), e2e with host buffers, and its deviation from a single-GPU run
+  c4_direct_sample         ONE direct-kernel pass at that geometry (ns = 5e6; 5.5 min in full)
+                           over two waves of strided 512-point tiles per rank, with its own
+                           roofline fraction and an oracle check at sampled points
+  cpu_baseline (N = 1)     the oracle (C restatement of the reference) on the host cores
+
+`--workload c2|c4|c5|c3|...` runs a single workload instead (with `--method direct|tree`).
+`--impl reference`: the reference's CPU algorithm (the oracle; the Fortran reference cannot be
+compiled in this image) on all host cores AND on one thread, on a bounded sample.
 """
 from __future__ import annotations
 
@@ -39,8 +45,9 @@ WORKLOADS = {
     "c2": (1_000_000, 0.05, 3, "single series n=1e6 f=0.05 nsteps=3 (BASELINE configs[1])"),
     "c2ref": (1_000_000, 0.05, 2, "single series n=1e6 f=0.05 nsteps=2 (reference smooth() default)"),
     "c5": (2_000_000, 0.8, 5, "wide span n=2e6 f=0.8 nsteps=5 (BASELINE configs[4])"),
-    "c4": (100_000_000, 0.05, 3, "single series n=1e8 f=0.05 nsteps=3 (BASELINE headline; >15 min/step)"),
+    "c4": (100_000_000, 0.05, 3, "single series n=1e8 f=0.05 nsteps=3 (BASELINE headline)"),
     "small": (100_000, 0.05, 3, "development size n=1e5 f=0.05 nsteps=3"),
+    "mid": (4_000_000, 0.05, 3, "development size n=4e6 f=0.05 nsteps=3"),
 }
 # batched workloads: name -> (nseries, n, f, nsteps, description)
 BATCHED = {
@@ -48,13 +55,13 @@ BATCHED = {
     "c3small": (256, 16384, 0.3, 2, "development: 256 series x n=16384 f=0.3 nsteps=2"),
 }
 FLOP_PER_PAIR = 17.0
+TILE = 512                # output points per tile of the direct kernel
 # dram__bytes_read.sum + dram__bytes_write.sum of one fit_kernel launch, from the committed
 # `ncu --set full` captures (profiles/README.md); None where no capture exists.
 NCU_TRAFFIC = {
-    "c2": {"bytes": 48.5e6 + 349.2e6, "from": "profiles/r01_fit_kernel_c2_ncu_full.csv (mean of 2 launches; K=10 "
-                                              "window split writes 400 MB of partial moments; 0.15% of DRAM peak)"},
+    "c2": {"bytes": 48.5e6 + 349.2e6, "from": "profiles/r01_fit_kernel_c2_ncu_full.csv (mean of 2 launches; the K=10 "
+                                              "window split writes 350 MB of partial moments; 0.15% of DRAM peak)"},
 }
-BYTES_PER_POINT_PASS = 56.0
 
 
 def parse():
@@ -63,13 +70,12 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS) + sorted(BATCHED))
-    ap.add_argument("--method", default="direct", choices=["direct", "tree", "auto"],
-                    help="evaluator of a lowest() pass: direct O(n ns) kernel (roofline claim) or moment tree")
+    ap.add_argument("--workload", default="default", choices=["default"] + sorted(WORKLOADS) + sorted(BATCHED))
+    ap.add_argument("--method", default=None, choices=["direct", "tree", "auto"],
+                    help="evaluator of a lowest() pass (single-workload runs): direct O(n ns) kernel or moment tree")
     ap.add_argument("--transport", default="p2p", choices=["p2p", "nccl"],
                     help="N > 1: exchange of the robustness step -- kernels over NVLink peer memory, or NCCL")
-    ap.add_argument("--no-tree", action="store_true",
-                    help="N = 1: skip the extra moment-tree measurements (same workload and n=1e8)")
+    ap.add_argument("--no-headline", action="store_true", help="default run: skip the n = 1e8 part")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -82,70 +88,110 @@ def make_data(n):
     return x, y
 
 
+def series_config(name, method, world, transport):
+    """The `config` object of a single-series workload; both arms print the same one."""
+    n, f, nsteps, wname = WORKLOADS[name]
+    ns = max(min(int(f * float(n)), n), 2)
+    return {"workload": wname, "n": n, "f": f, "nsteps": nsteps, "ns": ns,
+            "x": "grid (i-1)*dx", "y": "0.5sin20x+cos5x*exp(-.1x)+U(-.5,.5) splitmix64",
+            "l2": "256 MiB flush write between timed steps",
+            "parallelism": f"range-sharded x{world}" if world > 1 else "single GPU",
+            "method": method, "transport": transport if world > 1 else "none"}
+
+
 # ----------------------------------------------------------------------------
 # CPU arm: the oracle on the host cores, on a bounded sample of output points
 # ----------------------------------------------------------------------------
-def cpu_sample(x, y, f, nsteps, seconds_target=6.0):
-    """Times the oracle's lowest() (all host threads, OpenMP over points) on a
-    stratified sample of output points: one unweighted and one weighted pass.
-    Returns (points_per_sec for a full smooth, cores, sample description)."""
+def cpu_sample(x, y, f, nsteps, threads, seconds_target=6.0, robust=True):
+    """Times the oracle's lowest() on `threads` host threads (OpenMP over points; set
+    explicitly -- launchers export OMP_NUM_THREADS=1) over a stratified sample of output
+    points, one unweighted and one weighted pass, and the robustness step (|res| full sort +
+    bisquare, single-threaded like the reference) in full, and extrapolates one smooth():
+        t = n * (t_unweighted + nsteps * t_weighted) / m + nsteps * t_robust."""
     from oracle import oracle
     n = x.size
-    cores = oracle.max_threads()
+    threads = oracle.set_threads(threads)
     ns = oracle.span(n, f)
     rw = np.ones(n)
-    m = max(cores * 32, 64)
-    # calibrate m so that one sample pass lasts about seconds_target / 2
+    m = max(threads * 8, 16)
     idx = np.linspace(0, n - 1, m).astype(np.int32)
     t0 = time.perf_counter()
-    oracle.lowest_at(x, y, f, idx, None)
+    oracle.lowest_at(x, y, f, idx, None)           # calibration (also warms the caches)
     dt = time.perf_counter() - t0
     m = int(min(max(m * (seconds_target / 2) / max(dt, 1e-4), m), 200000, n))
     idx = np.linspace(0, n - 1, m).astype(np.int32)
     t0 = time.perf_counter()
-    oracle.lowest_at(x, y, f, idx, None)          # pass 1: userw = .false.
+    ya = oracle.lowest_at(x, y, f, idx, None)      # pass 1: userw = .false.
     t1 = time.perf_counter()
-    oracle.lowest_at(x, y, f, idx, rw)            # later passes: userw = .true.
+    oracle.lowest_at(x, y, f, idx, rw)             # later passes: userw = .true.
     t2 = time.perf_counter()
-    per_point = ((t1 - t0) + nsteps * (t2 - t1)) / m   # seconds per output point per smooth
-    pps = 1.0 / per_point
-    ns_per_pair = ((t2 - t0) / 2) / m / ns * cores * 1e9
-    desc = (f"{m} stratified output points x 2 passes (1 unweighted, 1 weighted) of n={n} ns={ns}, "
-            f"oracle lowest() on {cores} threads, extrapolated to {nsteps + 1} passes; "
-            f"{ns_per_pair:.2f} ns/pair/core; |res| sort not included")
-    return pps, cores, desc, (t2 - t0)
+    t_rob = t_rob_measured = 0.0
+    if robust and nsteps > 0:
+        res = y - np.interp(x, x[idx], ya["ys"])   # residual-like values; only their sort cost matters
+        nr = min(n, 4_000_000)                     # bounded: n log n scaling applied above that
+        t3 = time.perf_counter()
+        oracle.robust_weights(res[:nr])
+        t_rob = t_rob_measured = time.perf_counter() - t3
+        if nr < n:
+            t_rob *= (n * np.log2(n)) / (nr * np.log2(nr))
+    fit_s = n * ((t1 - t0) + nsteps * (t2 - t1)) / m
+    total_s = fit_s + nsteps * t_rob
+    ns_per_pair = ((t2 - t0) / 2) / m / ns * threads * 1e9
+    desc = (f"{m} stratified output points x 2 passes (1 unweighted, 1 weighted) of n={n} ns={ns}, oracle "
+            f"lowest() on {threads} thread(s), extrapolated to {nsteps + 1} passes; {ns_per_pair:.2f} ns/pair/core; "
+            f"+ {nsteps} x the |res| sort + bisquare step ({t_rob * 1e3:.0f} ms each, single thread"
+            f"{', scaled n log n from 4e6' if robust and n > 4_000_000 else ''})")
+    return {"value": n / total_s, "cores": threads, "sample": desc, "measured_s": (t2 - t0) + t_rob_measured,
+            "extrapolated_smooth_s": total_s, "ns_per_pair_per_core": ns_per_pair}
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    n, f, nsteps, wname = WORKLOADS[args.workload]
+    name = "c2" if args.workload == "default" else args.workload
+    n, f, nsteps, wname = WORKLOADS[name]
     x, y = make_data(n)
     from oracle import oracle
     oracle.build()
-    vals, desc, cores = [], "", 1
-    target = 3.0
-    for _ in range(max(args.warmup, 1)):
-        cpu_sample(x, y, f, nsteps, 1.0)
-    t_all = 0.0
-    for _ in range(args.steps):
-        pps, cores, desc, dt = cpu_sample(x, y, f, nsteps, target)
-        vals.append(pps)
-        t_all += dt
-    v = float(np.median(vals))
+    cores = oracle.host_cores()
+    world = int(os.environ.get("WORLD_SIZE", str(args.gpus)))
+    method = args.method or "direct"
+    for _ in range(max(min(args.warmup, 2), 1)):
+        cpu_sample(x, y, f, nsteps, cores, 0.5, robust=False)
+    t_wall = time.perf_counter()
+    runs = [cpu_sample(x, y, f, nsteps, cores, 3.0) for _ in range(max(1, min(args.steps, 5)))]
+    runs.sort(key=lambda r: r["value"])
+    allc = runs[len(runs) // 2]
+    one = cpu_sample(x, y, f, nsteps, 1, 4.0)
+    wall = time.perf_counter() - t_wall
+    v = allc["value"]
     line = {
         "impl": "reference", "metric": "LOWESS fitted points/sec", "value": v, "unit": "points/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * n / v, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": wname, "n": n, "f": f, "nsteps": nsteps},
-        "cpu_baseline": {"value": v, "unit": "points/s", "cores": cores, "kind": "port", "sample": desc},
+        "config": series_config(name, method, world, args.transport),
+        "cpu_baseline": {"value": v, "unit": "points/s", "cores": allc["cores"], "kind": "port",
+                         "sample": allc["sample"]},
+        "single_thread": {"value": one["value"], "unit": "points/s", "cores": 1, "sample": one["sample"],
+                          "note": "the reference's real execution model: no OpenMP anywhere (CMakeLists.txt:114)"},
         "e2e": {"value": v, "unit": "points/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "timed_region": {"measured_sample_s_per_step": allc["measured_s"], "wall_s_all_steps": wall,
+                         "ms_per_step_is": "EXTRAPOLATED full smooth() = n/m x sample passes + nsteps x |res| sort"},
         "gpu_launches": 0,
-        "note": "oracle = C restatement of the reference (no Fortran compiler in this image); "
-                "ms_per_step is the extrapolated full smooth()",
+        "note": "oracle = C restatement of the reference (no Fortran compiler in this image); value = all host "
+                "cores (OpenMP over output points, thread count set explicitly), single_thread beside it",
     }
+    if args.workload == "default" and not args.no_headline:
+        # the metric's own configuration: a handful of points at ns = 5e6 (36 ms per point per core)
+        n4, f4, k4, _ = WORKLOADS["c4"]
+        x4 = np.arange(n4, dtype=np.float64) * (1.0 / (n4 - 1.0))
+        y4 = np.sin(20.0 * x4)
+        r4 = cpu_sample(x4, y4, f4, k4, cores, 3.0, robust=False)
+        line["headline_n1e8"] = {"value": r4["value"], "unit": "points/s", "cores": r4["cores"],
+                                 "extrapolated_smooth_s": r4["extrapolated_smooth_s"], "sample": r4["sample"],
+                                 "note": "direct O(n ns) algorithm of the reference; the |res| sort is not included"}
     print(json.dumps(line), flush=True)
 
 
@@ -196,246 +242,325 @@ class Clocks:
 # ----------------------------------------------------------------------------
 # GPU arm
 # ----------------------------------------------------------------------------
-def run_ours(args):
-    import ctypes as C
+class Env:
+    def __init__(self, args):
+        import torch
+        import torch.distributed as dist
 
-    import torch
-    import torch.distributed as dist
+        from curvefit_b200 import _lib
+        self.torch, self.dist = torch, dist
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(self.local)
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+        self.lib = _lib.load()
+        self.flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
+        self.args = args
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, vals):
+        if self.world == 1:
+            return [float(v) for v in vals]
+        t = self.torch.tensor(list(vals), device="cuda", dtype=self.torch.float64)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return [float(v) for v in t.tolist()]
+
+    def pinned(self, a):
+        return self.torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()
+
+    def pinned_empty(self, n):
+        return self.torch.empty(n, dtype=self.torch.float64).pin_memory().numpy()
+
+
+def measure_series(env, name, method, steps, warmup, want_e2e, clocks=None, sample_direct=False,
+                   compare_single=False):
+    """One single-series workload, range-sharded over the ranks: device-resident steps (CUDA
+    events, L2 flush between steps, max over ranks), per-stage times, optional e2e with host
+    buffers, optional comparison with a single-GPU run, optional sampled direct-kernel pass."""
+    import ctypes as C
 
     from curvefit_b200 import _lib, lowess_smoothing, regression
     from curvefit_b200.distributed import DeviceStages, ShardedLowess, torch_stream_handle
-
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    n, f, nsteps, wname = WORKLOADS[args.workload]
+    torch, lib, args = env.torch, env.lib, env.args
+    world, rank = env.world, env.rank
+    n, f, nsteps, wname = WORKLOADS[name]
     x, y = make_data(n)
-    if args.method != "direct":
-        os.environ["CF_LOWESS_METHOD"] = args.method     # the stateless e2e calls use it too
-    lib = _lib.load()
     ns = lib.cf_lowess_span(n, f)
-
     stream = torch_stream_handle()
-    fit = lowess_smoothing(device=local, stream=stream)
-    fit.set_method(args.method)
+    fit = lowess_smoothing(device=env.local, stream=stream)
+    fit.set_method(method)
     fit.initialize(x, y, srt=False)           # resident in HBM from here on
     stages = DeviceStages(fit, rank, world)
     transport = "none"
     if world > 1:
         transport = "p2p" if (args.transport == "p2p" and stages.attach_peers()) else "nccl"
     job = ShardedLowess(stages)
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
 
     def step():
         if world == 1:
             return fit.run_resident(f, nsteps)
         lib.cf_lowess_reset_windows(fit._h)       # a step is a complete smooth(): windows included
-        job.run(f, nsteps, gather=True)
-        return None
+        job.run(f, nsteps, gather=False)          # every rank ends up holding its block of ys, rw, res
+        return job.last_stats
 
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         step()
-    peak_tf, peak_mhz = regression.fp64_peak(local, 300.0) if rank == 0 else (0.0, 0.0)
-    barrier()
-
-    ms_steps, fit_ms, fit_launches, launches = [], 0.0, 0, 0
-    with Clocks(local) as clk:
-        for _ in range(args.steps):
-            flush.fill_(1)
-            barrier()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            l0 = lib.cf_lowess_launch_count(fit._h)
-            e0.record()
-            st = step()
-            e1.record()
-            barrier()
-            ms = e0.elapsed_time(e1)
-            if world > 1:
-                t = torch.tensor([ms], device="cuda", dtype=torch.float64)
-                dist.all_reduce(t, op=dist.ReduceOp.MAX)
-                ms = float(t.item())
-            ms_steps.append(ms)
-            if st is not None:
-                fit_ms += st.ms_fit
-                fit_launches += st.fit_launches
-            launches += lib.cf_lowess_launch_count(fit._h) - l0
+    env.barrier()
+    ms_steps, launches = [], 0
+    stage = {"windows": 0.0, "fit": 0.0, "robust": 0.0, "tree_build": 0.0}
+    fit_launches = 0
+    for _ in range(steps):
+        env.flush.fill_(1)
+        env.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = lib.cf_lowess_launch_count(fit._h)
+        e0.record()
+        st = step()
+        e1.record()
+        env.barrier()
+        vals = [e0.elapsed_time(e1)]
+        if st is not None:
+            vals += [st.ms_windows, st.ms_fit, st.ms_robust, st.ms_tree_build]
+        vals = env.max_over_ranks(vals)
+        ms_steps.append(vals[0])
+        if st is not None:
+            for k, v in zip(("windows", "fit", "robust", "tree_build"), vals[1:]):
+                stage[k] += v
+            fit_launches += st.fit_launches
+        launches += lib.cf_lowess_launch_count(fit._h) - l0
     total_ms = float(sum(ms_steps))
-    value = n * args.steps / (total_ms * 1e-3)
-    if world > 1 and stages.p2p and stages.peer_error():
-        raise RuntimeError("a peer-memory wait timed out during the timed region")
+    if world > 1:
+        job.check_all()
+    out = {"workload": wname, "method": method, "transport": transport,
+           "value": n * steps / (total_ms * 1e-3), "unit": "points/s", "n_gpus": world,
+           "ms_per_step": total_ms / steps, "steps": steps, "warmup": warmup,
+           "ms_min_max": [min(ms_steps), max(ms_steps)],
+           "stages_ms_per_step": {k: v / steps for k, v in stage.items()} if fit_launches else None,
+           "stages_note": "CUDA events inside cf_lowess_run, max over ranks; tree_build is part of fit; "
+                          "result left sharded (each rank holds its block of ys, rw, res)",
+           "gpu_launches": launches, "fit_launches": fit_launches, "ns": ns}
+    out["_fit_ms"] = stage["fit"]
 
+    # ---- the sharded result against a single-GPU run of the same series (outside the timed region)
+    if world > 1 and compare_single:
+        job.gather_results(with_rw=True)
+        torch.cuda.synchronize()
+        if rank == 0:
+            solo = lowess_smoothing(device=env.local)
+            solo.set_method(method)
+            solo.initialize(x, y, srt=False)
+            t0 = time.perf_counter()
+            solo.run_resident(f, nsteps)
+            st1 = solo.run_resident(f, nsteps)
+            ys1, ysN = np.empty(n), np.empty(n)
+            lib.cf_lowess_fetch(solo._h, regression._dp(ys1), None, None)
+            lib.cf_lowess_fetch(fit._h, regression._dp(ysN), None, None)
+            d = float(np.max(np.abs(ys1 - ysN)))
+            out["vs_single_gpu"] = {"max_abs_diff_ys": d, "bitwise_equal_ys": bool(np.array_equal(ys1, ysN)),
+                                    "max_abs_ys": float(np.max(np.abs(ys1))),
+                                    "single_gpu_ms_same_box": float(st1.ms_total),
+                                    "speedup_vs_single_gpu_same_box": float(st1.ms_total) / out["ms_per_step"]}
+            assert d <= 1e-12 * max(out["vs_single_gpu"]["max_abs_ys"], 1.0), f"sharded ys differs by {d}"
+            solo.close()
+            del ys1, ysN
+        env.barrier()
+
+    # ---- e2e: HOST buffers in, HOST buffers out, copies inside the timed region ---------------
+    if want_e2e and world == 1:
+        xp, yp = env.pinned(x), env.pinned(y)
+        outs = tuple(env.pinned_empty(n) for _ in range(3))
+        regression.set_default_method(method)
+        try:
+            regression.cf_lowess_smooth(xp, yp, f, nsteps, out=outs)      # warm-up
+            reps = max(1, min(steps, 3))
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                regression.cf_lowess_smooth(xp, yp, f, nsteps, out=outs)
+            torch.cuda.synchronize()
+            dt = (time.perf_counter() - t0) / reps
+        finally:
+            regression.set_default_method("direct")
+        out["e2e"] = {"value": n / dt, "unit": "points/s", "h2d_bytes_per_step": 16 * n,
+                      "d2h_bytes_per_step": 24 * n, "ms_per_step": dt * 1e3,
+                      "api": "cf_lowess_smooth(host x, y -> host ys, rw, res), pinned buffers, wall clock"}
+        del xp, yp, outs
+    elif want_e2e:
+        xp, yp = env.pinned(x), env.pinned(y)
+        outs = tuple(env.pinned_empty(n) for _ in range(3)) if rank == 0 else None
+        job.smooth_host(xp, yp, f, nsteps, outs)
+        reps = max(1, min(steps, 3))
+        env.barrier()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            job.smooth_host(xp, yp, f, nsteps, outs)
+        env.barrier()
+        dt = env.max_over_ranks([(time.perf_counter() - t0) / reps])[0]
+        out["e2e"] = {"value": n / dt, "unit": "points/s", "h2d_bytes_per_step": 16 * n * world,
+                      "d2h_bytes_per_step": 24 * n, "ms_per_step": dt * 1e3,
+                      "api": "ShardedLowess.smooth_host(host x, y on every rank -> host ys, rw, res on "
+                             "rank 0), pinned buffers, wall clock, max over ranks"}
+        del xp, yp, outs
+    else:
+        out["e2e"] = None
+
+    # ---- one DIRECT-kernel pass at this geometry on a strided sample of tiles ---------------------
+    if sample_direct:
+        out["_direct_sample"] = direct_sample(env, fit, stages, x, y, n, f, ns)
+
+    if world > 1:
+        stages.detach_peers()
+    fit.close()
+    return out
+
+
+def direct_sample(env, fit, stages, x, y, n, f, ns):
+    """Every rank runs ONE weighted pass of the direct kernel (K = 1, as a full pass at this size
+    would) over two waves of 512-point tiles spread evenly over its shard, with the robustness
+    weights the preceding smooth left on the device.  Rate and roofline fraction come from the
+    slowest rank; rank 0 checks sampled points against the oracle's lowest()."""
+    from curvefit_b200 import regression
+    world, rank = env.world, env.rank
+    begin, end = stages.begin, stages.end
+    tiles_shard = max((end - begin + TILE - 1) // TILE, 1)
+    ntiles = min(2 * 148 * 4, tiles_shard)
+    stride = max(tiles_shard // ntiles, 1)
+    peak_tf, peak_mhz = regression.fp64_peak(env.local, 300.0)
+    env.barrier()
+    ms, idx, ys = fit.fit_sample(f, True, stride // 2, stride, ntiles)
+    vals = env.max_over_ranks([ms, -peak_tf])
+    ms_max, peak_min = vals[0], -vals[1]
+    pts = ntiles * TILE                           # per rank
+    tf_gpu = FLOP_PER_PAIR * pts * ns / (ms_max * 1e-3) / 1e12
+    full_pass_s = (tiles_shard / ntiles) * ms_max * 1e-3
+    res = {"kernel": "cf::fit_kernel (K = 1, no window split)", "n": n, "ns": ns, "n_gpus": world,
+           "tiles_per_rank": ntiles, "tile_stride": stride, "points_per_rank": pts, "ms": ms_max,
+           "roofline": {"bound": "fp64", "achieved": tf_gpu, "peak": peak_min, "unit": "TFLOP/s",
+                        "frac": tf_gpu / peak_min if peak_min else None, "traffic": None,
+                        "algorithmic": "17 flop/pair x sampled points x ns, per GPU, slowest rank",
+                        "peak_source": "cf_fp64_peak DFMA microbenchmark, min over ranks"},
+           "points_per_s_all_gpus": pts * world / (ms_max * 1e-3),
+           "extrapolated": {"one_pass_s": full_pass_s, "smooth_s_nsteps3": 4 * full_pass_s,
+                            "points_per_s_smooth": n / (4 * full_pass_s),
+                            "note": "every tile costs the same (ns + 512 staged elements x 512 points), so a full pass "
+                                    "= tiles/sampled tiles x this launch; the O(n) stages add < 0.01 %"}}
+    if rank == 0:
+        from oracle import oracle
+        oracle.build()
+        oracle.set_threads(oracle.host_cores())
+        rw = np.empty(n)
+        env.lib.cf_lowess_fetch(fit._h, None, regression._dp(rw), None)
+        pick = np.unique(np.linspace(0, idx.size - 1, 24).astype(np.int64))
+        t = oracle.lowest_at(x, y, f, idx[pick].astype(np.int32), rw)
+        d = np.abs(ys[pick] - t["ys"])
+        scale = float(np.max(np.abs(t["ys"])))
+        res["oracle_check"] = {"points": int(pick.size), "max_abs_diff": float(d.max()),
+                               "max_rel_to_scale": float(d.max() / scale), "tolerance": 1e-10,
+                               "ok": bool(d.max() <= 1e-10 * scale)}
+        assert res["oracle_check"]["ok"], res["oracle_check"]
+    return res
+
+
+def run_ours(args):
+    from curvefit_b200 import regression
+    env = Env(args)
+    rank, world = env.rank, env.world
+    single = args.workload != "default"
+    name = args.workload if single else "c2"
+    method = args.method or ("direct" if not single or name != "c4" else "tree")
+    n, f, nsteps, wname = WORKLOADS[name]
+    peak_tf, peak_mhz = regression.fp64_peak(env.local, 300.0)
+    peak_tf = -env.max_over_ranks([-peak_tf])[0]
+
+    with Clocks(env.local) as clk:
+        prim = measure_series(env, name, method, args.steps, args.warmup, not args.no_e2e,
+                              sample_direct=single and name == "c4" and method != "direct",
+                              compare_single=True)
     line = None
     if rank == 0:
+        ns = prim["ns"]
         line = {
-            "metric": "LOWESS fitted points/sec", "value": value, "unit": "points/s", "n_gpus": world,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
+            "metric": "LOWESS fitted points/sec", "value": prim["value"], "unit": "points/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": prim["ms_per_step"],
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
-            "config": {"workload": wname, "n": n, "f": f, "nsteps": nsteps, "ns": ns,
-                       "x": "grid (i-1)*dx", "y": "0.5sin20x+cos5x*exp(-.1x)+U(-.5,.5) splitmix64",
-                       "l2": "256 MiB flush write between timed steps",
-                       "parallelism": f"range-sharded x{world}" if world > 1 else "single GPU",
-                       "method": args.method, "transport": transport},
+            "config": series_config(name, method, world, args.transport),
+            "transport_used": prim["transport"],
             "gpu_launches_note": "kernels of libcurvefit_cuda launched by rank 0 inside the timed region",
-            "gpu_launches": launches,
+            "gpu_launches": prim["gpu_launches"],
             "clocks": clk.summary(),
+            "stages_ms_per_step": prim["stages_ms_per_step"],
+            "e2e": prim["e2e"],
         }
-        if world == 1 and fit_launches and args.method != "direct":
-            line["roofline"] = {
-                "bound": "fp64", "achieved": None, "peak": peak_tf, "unit": "TFLOP/s", "frac": None,
-                "traffic": None, "kernel": "fit stage = per-pass tree rebuild (cf::tree_block_kernel ...) + cf::tree_eval_kernel",
-                "avg_launch_ms": fit_ms / fit_launches, "share_of_step": fit_ms / total_ms,
-                "note": "moment-tree evaluator: O(n log ns) work, no 17 flop/pair accounting applies; "
-                        "ncu: profiles/r01_tree_eval_c4_ncu_full.csv (FP64 pipe 52% active, l1tex 73%). The roofline "
-                        "claim of this repo is the direct kernel's (default --method direct)."}
-        elif world == 1 and fit_launches:
-            avg_ms = fit_ms / fit_launches
-            flops = FLOP_PER_PAIR * n * ns
+        if "vs_single_gpu" in prim:
+            line["vs_single_gpu"] = prim["vs_single_gpu"]
+        if prim["fit_launches"] and method == "direct":
+            avg_ms = prim["_fit_ms"] / prim["fit_launches"]
+            flops = FLOP_PER_PAIR * (n / world) * ns          # per GPU: its shard of output points
             ach = flops / (avg_ms * 1e-3) / 1e12
             line["roofline"] = {
                 "bound": "fp64", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s",
                 "frac": ach / peak_tf if peak_tf else None,
-                "traffic": NCU_TRAFFIC.get(args.workload, {}).get("bytes"),
-                "traffic_source": NCU_TRAFFIC.get(args.workload, {}).get("from"),
-                "kernel": "cf::fit_kernel", "avg_launch_ms": avg_ms,
-                "share_of_step": fit_ms / total_ms,
+                "traffic": NCU_TRAFFIC.get(name, {}).get("bytes") if world == 1 else None,
+                "traffic_source": NCU_TRAFFIC.get(name, {}).get("from") if world == 1 else None,
+                "kernel": "cf::fit_kernel", "avg_launch_ms": avg_ms, "per_gpu": True,
+                "share_of_step": prim["_fit_ms"] / (prim["ms_per_step"] * prim["steps"]),
                 "peak_source": f"measured here: cf_fp64_peak DFMA microbenchmark ({peak_mhz:.0f} MHz equiv.; "
-                               "MEASURED_PEAKS.json has no FP64 figure); nominal 37.2 TFLOP/s at 1965 MHz",
-                "algorithmic": "17 flop/pair x n x ns pairs per launch (SURVEY 8d); the kernel issues "
-                               "10 FP64 instr/pair so 100% pipe use = 85% of this flop peak",
-                "hbm": {"algorithmic_bytes_per_launch": 24.0 * n + 8.0 * n,
-                        "gbs": (32.0 * n) / (avg_ms * 1e-3) / 1e9},
+                               "MEASURED_PEAKS.json has no FP64 figure), min over ranks; nominal 37.2 TFLOP/s at 1965 MHz",
+                "algorithmic": "17 flop/pair x (n / n_gpus) x ns pairs per launch (SURVEY 8d); the kernel issues "
+                               "10 FP64 instr/pair so 100% pipe use = 85% of this flop peak; avg_launch_ms is the "
+                               "slowest rank's (finalize of the window split included)",
+                "hbm": {"algorithmic_bytes_per_launch": 32.0 * n / world,
+                        "gbs": (32.0 * n / world) / (avg_ms * 1e-3) / 1e9},
             }
+        elif prim["fit_launches"]:
+            line["roofline"] = {
+                "bound": "fp64", "achieved": None, "peak": peak_tf, "unit": "TFLOP/s", "frac": None, "traffic": None,
+                "kernel": "fit stage = per-pass tree rebuild (cf::tree_block_kernel ...) + cf::tree_eval_kernel",
+                "avg_launch_ms": prim["_fit_ms"] / prim["fit_launches"],
+                "note": "moment-tree evaluator: O(n log ns) work, the 17 flop/pair accounting does not apply; the "
+                        "roofline claim of this repo is the direct kernel's (c4_direct_sample, or --method direct)"}
+        if "_direct_sample" in prim:
+            line["c4_direct_sample"] = prim["_direct_sample"]
 
-    # ---- e2e: host buffers through the stateless C ABI -------------------------------
-    if world == 1 and not args.no_e2e:
-        xp = torch.from_numpy(x).pin_memory().numpy()
-        yp = torch.from_numpy(y).pin_memory().numpy()
-        outs = tuple(torch.empty(n, dtype=torch.float64).pin_memory().numpy() for _ in range(3))
-        regression.cf_lowess_smooth(xp, yp, f, nsteps, out=outs)      # warm-up
-        reps = max(1, min(args.steps, 3))
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        for _ in range(reps):
-            regression.cf_lowess_smooth(xp, yp, f, nsteps, out=outs)
-        torch.cuda.synchronize()
-        dt = (time.perf_counter() - t0) / reps
-        line["e2e"] = {"value": n / dt, "unit": "points/s", "h2d_bytes_per_step": 16 * n,
-                       "d2h_bytes_per_step": 24 * n, "ms_per_step": dt * 1e3,
-                       "api": "cf_lowess_smooth(host x, y -> host ys, rw, res), pinned buffers, wall clock"}
-    elif world > 1 and not args.no_e2e:
-        # every rank uploads the series from pinned host memory, the ranks smooth it together,
-        # rank 0 reads ys, rw, res back -- all inside the timed region, max over ranks
-        xp = torch.from_numpy(x).pin_memory().numpy()
-        yp = torch.from_numpy(y).pin_memory().numpy()
-        outs = tuple(torch.empty(n, dtype=torch.float64).pin_memory().numpy() for _ in range(3)) if rank == 0 else None
-        job.smooth_host(xp, yp, f, nsteps, outs)
-        reps = max(1, min(args.steps, 3))
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(reps):
-            job.smooth_host(xp, yp, f, nsteps, outs)
-        barrier()
-        t = torch.tensor([(time.perf_counter() - t0) / reps], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dt = float(t.item())
+    # ---- the metric's own configuration: n = 1e8, f = 0.05, nsteps = 3, moment tree, at this N ----
+    if not single and not args.no_headline:
+        hsteps = max(3, min(args.steps, 10))
+        head = measure_series(env, "c4", "tree", hsteps, 3, not args.no_e2e, sample_direct=True,
+                              compare_single=True)
         if rank == 0:
-            line["e2e"] = {"value": n / dt, "unit": "points/s", "h2d_bytes_per_step": 16 * n * world,
-                           "d2h_bytes_per_step": 24 * n, "ms_per_step": dt * 1e3,
-                           "api": "ShardedLowess.smooth_host(host x, y on every rank -> host ys, rw, res on "
-                                  "rank 0), pinned buffers, wall clock, max over ranks"}
-    elif rank == 0:
-        line["e2e"] = None
-
-    # ---- moment-tree evaluator beside the direct kernel (N = 1 only) -----------------------
-    # Own accounting: never part of `value` or of the direct kernel's roofline.
-    if world == 1 and args.method == "direct" and not args.no_tree:
-        line["tree"] = tree_numbers(args, fit, flush, x, y, f, nsteps)
+            sample = head.pop("_direct_sample", None)
+            head.pop("_fit_ms", None)
+            head["config"] = series_config("c4", "tree", world, args.transport)
+            head["note"] = ("moment-tree evaluator (csrc/tree.cu): the same five sums per point from per-block power "
+                            "moments, equal to the direct kernel to rounding (tolerance 1e-10; tests/test_gpu_tree.py); "
+                            "separate accounting from `value` / `roofline`")
+            line["headline_n1e8"] = head
+            line["c4_direct_sample"] = sample
 
     # ---- CPU baseline on the host cores (rank 0, N = 1 only) ----------------------------
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         from oracle import oracle
         oracle.build()
-        pps, cores, desc, _ = cpu_sample(x, y, f, nsteps, 12.0)
-        line["cpu_baseline"] = {"value": pps, "unit": "points/s", "cores": cores, "kind": "port",
-                                "sample": desc}
+        x, y = make_data(n)
+        allc = cpu_sample(x, y, f, nsteps, oracle.host_cores(), 10.0)
+        one = cpu_sample(x, y, f, nsteps, 1, 5.0)
+        line["cpu_baseline"] = {"value": allc["value"], "unit": "points/s", "cores": allc["cores"], "kind": "port",
+                                "sample": allc["sample"],
+                                "single_thread": {"value": one["value"], "cores": 1, "sample": one["sample"]}}
     if rank == 0:
+        for k in [k for k in line if k.startswith("_")]:
+            line.pop(k)
         print(json.dumps(line), flush=True)
     if world > 1:
-        stages.detach_peers()
-        dist.barrier()
-        dist.destroy_process_group()
-
-
-def tree_numbers(args, fit, flush, x, y, f, nsteps):
-    """The O(n log ns) moment-tree evaluator (csrc/tree.cu) on the bench workload and on the
-    BASELINE headline series (n = 1e8, f = 0.05, 3 robustness iterations), device-resident,
-    CUDA-event timed per step with the L2 flush in between; plus its largest deviation from
-    the direct kernel's ys on the bench workload."""
-    import torch
-
-    from curvefit_b200 import lowess_smoothing
-    from curvefit_b200.regression import _dp
-
-    def timed(obj, ff, k, reps):
-        obj.run_resident(ff, k)
-        ms = []
-        for _ in range(reps):
-            flush.fill_(1)
-            torch.cuda.synchronize()
-            ms.append(obj.run_resident(ff, k).ms_total)
-        return float(np.median(ms))
-
-    out = {}
-    ys_direct = np.empty(x.size)
-    fit._lib.cf_lowess_fetch(fit._h, _dp(ys_direct), None, None)
-    fit.set_method("tree")
-    ms = timed(fit, f, nsteps, max(args.steps, 3))
-    ys_tree = np.empty(x.size)
-    fit._lib.cf_lowess_fetch(fit._h, _dp(ys_tree), None, None)
-    fit.set_method("direct")
-    out["same_workload"] = {"value": x.size / (ms * 1e-3), "unit": "points/s", "ms_per_step": ms,
-                            "max_abs_diff_vs_direct": float(np.max(np.abs(ys_tree - ys_direct))),
-                            "max_abs_ys": float(np.max(np.abs(ys_direct)))}
-    if not args.no_e2e:
-        # the same host-buffer C ABI call as `e2e`, with CF_LOWESS_METHOD=tree
-        from curvefit_b200 import regression
-        xp = torch.from_numpy(x).pin_memory().numpy()
-        yp = torch.from_numpy(y).pin_memory().numpy()
-        outs = tuple(torch.empty(x.size, dtype=torch.float64).pin_memory().numpy() for _ in range(3))
-        os.environ["CF_LOWESS_METHOD"] = "tree"
-        try:
-            regression.cf_lowess_smooth(xp, yp, f, nsteps, out=outs)
-            torch.cuda.synchronize()
-            t0 = time.perf_counter()
-            for _ in range(5):
-                regression.cf_lowess_smooth(xp, yp, f, nsteps, out=outs)
-            dt = (time.perf_counter() - t0) / 5
-        finally:
-            os.environ.pop("CF_LOWESS_METHOD", None)
-        out["same_workload"]["e2e"] = {"value": x.size / dt, "unit": "points/s", "ms_per_step": dt * 1e3,
-                                       "h2d_bytes_per_step": 16 * x.size, "d2h_bytes_per_step": 24 * x.size}
-    n4, f4, k4, name4 = WORKLOADS["c4"]
-    if x.size != n4:
-        x4, y4 = make_data(n4)
-        big = lowess_smoothing(device=fit._device, stream=fit._stream)
-        big.set_method("tree")
-        big.initialize(x4, y4, srt=False)
-        ms4 = timed(big, f4, k4, 2)
-        out["headline_n1e8"] = {"workload": name4.split(" (")[0], "value": n4 / (ms4 * 1e-3), "unit": "points/s",
-                                "ms_per_step": ms4}
-        big.close()
-    out["note"] = ("moment-tree evaluator, equal to the direct kernel to rounding (tolerance 1e-10); "
-                   "separate accounting from `value` / `roofline`")
-    return out
+        env.dist.barrier()
+        env.dist.destroy_process_group()
 
 
 # ----------------------------------------------------------------------------
@@ -458,7 +583,7 @@ def run_batched_reference(args):
     nseries, n, f, nsteps, wname = BATCHED[args.workload]
     from oracle import oracle
     oracle.build()
-    cores = oracle.max_threads()
+    cores = oracle.set_threads(oracle.host_cores())
     x, y = make_batched(2, n)
     oracle.lowess_mt(x[0], y[0], f, nsteps)
     vals = []
@@ -494,14 +619,14 @@ def run_batched(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     nseries, n, f, nsteps, wname = BATCHED[args.workload]
-    if args.method != "direct":
-        os.environ["CF_LOWESS_METHOD"] = args.method
+    method = args.method or "direct"
+    regression.set_default_method(method)
     mine = nseries // world            # series are independent: partition, no collective
     x, y = make_batched(mine, n, first=rank * mine)
     ns = _lib.load().cf_lowess_span(n, f)
     stream = torch_stream_handle()
     b = regression.batched_lowess(device=local, stream=stream)
-    b.set_method(args.method)
+    b.set_method(method)
     b.initialize(x, y)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 
@@ -553,8 +678,8 @@ def run_batched(args):
                          "share_of_step": fit_ms / total_ms,
                          "peak_source": f"measured here: cf_fp64_peak ({peak_mhz:.0f} MHz equiv.)"},
         }
-        line["config"]["method"] = args.method
-        if args.method != "direct":
+        line["config"]["method"] = method
+        if method != "direct":
             line["roofline"].update({"achieved": None, "frac": None,
                                      "kernel": "fit stage = per-pass tree rebuild (cf::tree_block_kernel ...) + cf::tree_eval_kernel",
                                      "note": "moment-tree evaluator: the 17 flop/pair accounting does not apply"})
@@ -572,10 +697,11 @@ def run_batched(args):
         if world == 1 and not args.no_cpu_baseline:
             from oracle import oracle
             oracle.build()
+            cores = oracle.set_threads(oracle.host_cores())
             t0 = time.perf_counter()
             oracle.lowess_mt(x[0], y[0], f, nsteps)
             dt = time.perf_counter() - t0
-            line["cpu_baseline"] = {"value": n / dt, "unit": "points/s", "cores": oracle.max_threads(),
+            line["cpu_baseline"] = {"value": n / dt, "unit": "points/s", "cores": cores,
                                     "kind": "port", "sample": "1 series in full, oracle lowess on all threads"}
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -27,6 +27,8 @@ class cf_stats(C.Structure):
         ("ns", C.c_int32),
         ("passes", C.c_int32),
         ("cmad_last", C.c_double),
+        ("ms_tree_build", C.c_float),
+        ("reserved", C.c_float),
     ]
 
 
@@ -58,12 +60,16 @@ SIGNATURES = {
     "cf_lowess_shard": (C.c_int32, [C.c_void_p, c_ip, c_ip, c_ip]),
     "cf_lowess_run": (C.c_int32, [C.c_void_p, C.c_double, C.c_int32, C.POINTER(cf_stats)]),
     "cf_lowess_run_from_rw": (C.c_int32, [C.c_void_p, C.c_double, c_dp, C.c_int32]),
+    "cf_lowess_fit_sample": (C.c_int32, [C.c_void_p, C.c_double, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
+                                         C.POINTER(C.c_float)]),
     "cf_lowess_fetch": (C.c_int32, [C.c_void_p, c_dp, c_dp, c_dp]),
     "cf_lowess_fetch_xy": (C.c_int32, [C.c_void_p, c_dp, c_dp]),
     "cf_lowess_count": (C.c_int32, [C.c_void_p]),
     "cf_lowess_launch_count": (C.c_int64, [C.c_void_p]),
     "cf_lowess_set_method": (C.c_int32, [C.c_void_p, C.c_int32]),
     "cf_lowess_method": (C.c_int32, [C.c_void_p]),
+    "cf_set_default_method": (C.c_int32, [C.c_int32]),
+    "cf_default_method": (C.c_int32, []),
     "cf_lowess_reset_windows": (C.c_int32, [C.c_void_p]),
     "cf_lowess_windows": (C.c_int32, [C.c_void_p, C.c_double, c_ip, c_ip, c_ip, c_ip, c_ip, c_ip, c_ip]),
     "cf_lowess_stage_begin": (C.c_int32, [C.c_void_p, C.c_double]),
@@ -75,6 +81,8 @@ SIGNATURES = {
     "cf_lowess_peer_handle_bytes": (C.c_int32, []),
     "cf_lowess_peer_export": (C.c_int32, [C.c_void_p, C.c_void_p]),
     "cf_lowess_peer_attach": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32]),
+    "cf_lowess_peer_attach_local": (C.c_int32, [C.POINTER(C.c_void_p), C.c_int32]),
+    "cf_lowess_peer_set_timeout": (C.c_int32, [C.c_void_p, C.c_double]),
     "cf_lowess_peer_detach": (C.c_int32, [C.c_void_p]),
     "cf_lowess_peer_attached": (C.c_int32, [C.c_void_p]),
     "cf_lowess_peer_error": (C.c_int32, [C.c_void_p, c_ip]),
@@ -82,12 +90,13 @@ SIGNATURES = {
     "cf_lowess_sync": (C.c_int32, [C.c_void_p]),
     "cf_lowess_buffer": (C.c_void_p, [C.c_void_p, C.c_int32]),
     "cf_lowess_hist_len": (C.c_int32, []),
+    "cf_lowess_hist0_len": (C.c_int32, []),
     "cf_fp64_peak": (C.c_int32, [C.c_int32, C.c_double, c_dp, c_dp]),
 }
 
 CF_GATHER_YS, CF_GATHER_RES, CF_GATHER_RW = 1, 2, 4
 CF_METHOD_DIRECT, CF_METHOD_TREE, CF_METHOD_AUTO = range(3)
-CF_BUF_X, CF_BUF_Y, CF_BUF_YS, CF_BUF_RW, CF_BUF_RES, CF_BUF_HIST, CF_BUF_CMAD = range(7)
+CF_BUF_X, CF_BUF_Y, CF_BUF_YS, CF_BUF_RW, CF_BUF_RES, CF_BUF_HIST, CF_BUF_CMAD, CF_BUF_HIST0 = range(8)
 
 _lib = None
 

@@ -8,6 +8,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <atomic>
 #include <mutex>
 #include <new>
 #include <vector>
@@ -62,16 +63,30 @@ static int reserve(cf_lowess* h, int32_t n, int32_t nseries = 1)
 {
     const int64_t need = (n > 0 ? (int64_t)n : 1) * (nseries > 0 ? nseries : 1);
     if (nseries > h->sel_cap) {
-        cudaFree(h->hist); cudaFree(h->sel); cudaFree(h->span);
-        h->hist = nullptr; h->sel = nullptr; h->span = nullptr; h->sel_cap = 0;
+        cudaFree(h->hist0); cudaFree(h->hist); cudaFree(h->sel); cudaFree(h->span);
+        h->hist0 = nullptr; h->hist = nullptr; h->sel = nullptr; h->span = nullptr; h->sel_cap = 0;
+        // sized for either geometry (one series: B0 = 15, W = 12; batched: 11, 11)
+        size_t b0 = (sizeof(unsigned int) << kSelB0Batched) * (size_t)nseries;
+        size_t bw = 2 * (sizeof(unsigned int) << kSelWBatched) * (size_t)nseries;
+        if (b0 < (sizeof(unsigned int) << kSelB0Single)) b0 = sizeof(unsigned int) << kSelB0Single;
+        if (bw < 2 * (sizeof(unsigned int) << kSelWSingle)) bw = 2 * (sizeof(unsigned int) << kSelWSingle);
         CF_CUDA(cudaMalloc(&h->span, sizeof(int32_t) * 2 * (size_t)nseries));
-        CF_CUDA(cudaMalloc(&h->hist, sizeof(unsigned long long) * kHistLen * (size_t)nseries));
+        CF_CUDA(cudaMalloc(&h->hist0, b0));
+        CF_CUDA(cudaMalloc(&h->hist, bw));
         CF_CUDA(cudaMalloc(&h->sel, sizeof(SelectState) * (size_t)nseries));
-        CF_CUDA(cudaMemsetAsync(h->hist, 0, sizeof(unsigned long long) * kHistLen * (size_t)nseries, h->stream));
-        CF_CUDA(cudaMemsetAsync(h->sel, 0, sizeof(SelectState) * (size_t)nseries, h->stream));
         h->sel_cap = nseries;
     }
+    {   // the select kernels leave their counters zeroed; start from zero whatever happened before
+        const SelGeom g = sel_geom(false, nseries > 1);
+        CF_CUDA(cudaMemsetAsync(h->hist0, 0, (sizeof(unsigned int) << g.b0) * (size_t)nseries, h->stream));
+        CF_CUDA(cudaMemsetAsync(h->hist, 0, 2 * (sizeof(unsigned int) << g.w) * (size_t)nseries, h->stream));
+        CF_CUDA(cudaMemsetAsync(h->sel, 0, sizeof(SelectState) * (size_t)nseries, h->stream));
+    }
     if (need > h->cap) {
+        if (h->peer_attached) {
+            set_error("the series grew while peers are attached: detach on all ranks first");
+            return CF_INVALID_INPUT_ERROR;
+        }
         free_buffers(h);
         const size_t bd = sizeof(double) * (size_t)need, bi = sizeof(int32_t) * (size_t)need;
         CF_CUDA(cudaMalloc(&h->x, bd));
@@ -97,7 +112,10 @@ static int reserve_rw(cf_lowess* h)
     if (h->nseries > 1) need = (int64_t)h->n * h->nseries;   // batched: no sharding inside a series
     if (need < 1) need = 1;
     if (need > h->cap_rw) {
-        peer_detach(h);
+        if (h->peer_attached) {
+            set_error("the series grew while peers are attached: detach on all ranks first");
+            return CF_INVALID_INPUT_ERROR;
+        }
         cudaFree(h->rw);
         h->rw = nullptr;
         h->cap_rw = 0;
@@ -114,13 +132,12 @@ static int use_device(const cf_lowess* h)
     return CF_OK;
 }
 
-static int robust_update(cf_lowess* h)
+// residuals (:695) fused with round 0 of the select, the select (:697-703), the weights (:704-713)
+static int residuals_and_robust_update(cf_lowess* h)
 {
-    CF_TRY(launch_select_reset(h));
-    for (int r = 0; r < kSelRounds; ++r) {
-        CF_TRY(launch_hist(h, r));
-        CF_TRY(launch_pick(h, r));
-    }
+    const bool fused = !(h->delta > 0.0);
+    if (!fused) CF_TRY(launch_residuals(h));       // delta > 0: interpolation + tie copy + residuals
+    CF_TRY(launch_select(h, fused));
     return launch_bisquare(h);
 }
 
@@ -142,15 +159,8 @@ static int begin_stage(cf_lowess* h, double f)
     return CF_OK;
 }
 
-// CF_LOWESS_METHOD = direct | tree | auto (default direct)
-static int method_from_env()
-{
-    const char* v = getenv("CF_LOWESS_METHOD");
-    if (!v) return CF_METHOD_DIRECT;
-    if (!strcmp(v, "tree")) return CF_METHOD_TREE;
-    if (!strcmp(v, "auto")) return CF_METHOD_AUTO;
-    return CF_METHOD_DIRECT;
-}
+// evaluator of handles created from now on and of the stateless calls (cf_set_default_method)
+static std::atomic<int> g_default_method{CF_METHOD_DIRECT};
 
 }  // namespace cf
 
@@ -183,8 +193,9 @@ int32_t cf_lowess_span(int32_t n, double f)
     return k;
 }
 
-int32_t cf_lowess_select_rounds(void) { return kSelRounds; }
-int32_t cf_lowess_hist_len(void) { return kHistLen; }
+int32_t cf_lowess_select_rounds(void) { return 1 + sel_geom(false, false).rounds; }
+int32_t cf_lowess_hist0_len(void) { return 1 << kSelB0Single; }
+int32_t cf_lowess_hist_len(void) { return 2 << kSelWSingle; }
 
 int32_t cf_lowess_create(cf_lowess** out, int32_t device, void* stream)
 {
@@ -203,9 +214,9 @@ int32_t cf_lowess_create(cf_lowess** out, int32_t device, void* stream)
     cf_lowess* h = new (std::nothrow) cf_lowess();
     if (!h) { set_error("Insufficient memory available."); return CF_OUT_OF_MEMORY_ERROR; }
     h->device = device;
-    if (const char* v = getenv("CF_FIT_VARIANT")) h->fit_variant = atoi(v);
-    if (const char* v = getenv("CF_FIT_KSPLIT")) h->ksplit_override = atoi(v);
-    h->method = method_from_env();
+    if (const char* v = dev_env("CF_FIT_VARIANT")) h->fit_variant = atoi(v);
+    if (const char* v = dev_env("CF_FIT_KSPLIT")) h->ksplit_override = atoi(v);
+    h->method = g_default_method.load();
     if (stream) {
         h->stream = (cudaStream_t)stream;
     } else {
@@ -232,7 +243,9 @@ void cf_lowess_destroy(cf_lowess* h)
     if (h->stream) cudaStreamSynchronize(h->stream);
     free_buffers(h);
     cudaFree(h->comm);
+    cudaFree(h->hist0);
     cudaFree(h->hist);
+    cudaFree(h->cand);
     cudaFree(h->sel);
     cudaFree(h->span);
     cudaFree(h->sort_aux);
@@ -358,6 +371,18 @@ int32_t cf_lowess_set_method(cf_lowess* h, int32_t method)
 
 int32_t cf_lowess_method(const cf_lowess* h) { return h ? h->method : -1; }
 
+int32_t cf_set_default_method(int32_t method)
+{
+    if (method < CF_METHOD_DIRECT || method > CF_METHOD_AUTO) {
+        set_error("bad method %d", (int)method);
+        return CF_INVALID_INPUT_ERROR;
+    }
+    g_default_method.store(method);
+    return CF_OK;
+}
+
+int32_t cf_default_method(void) { return g_default_method.load(); }
+
 int32_t cf_lowess_set_delta(cf_lowess* h, double delta)
 {
     if (!h || !(delta >= 0.0) || !(delta <= 1.7976931348623157e308)) {
@@ -414,6 +439,15 @@ extern "C" {
 // `passes` fit passes; the first uses rw iff first_uses_rw (lowess :657-714)
 static int32_t run_passes(cf_lowess* h, int32_t passes, bool first_uses_rw, cf_stats* st)
 {
+    if (h->nranks > 1 && !h->peer_attached && passes > 1) {
+        // the median and the weights of a robustness step need every shard: without attached
+        // peers (or a host runtime driving the stage calls) later passes would be silently wrong
+        set_error("handle holds shard %d of %d but no peers are attached: only single passes can run",
+                  (int)h->rank, (int)h->nranks);
+        return CF_INVALID_INPUT_ERROR;
+    }
+    CF_TRY(select_prepare(h));
+    CF_TRY(peer_clear_error(h));
     std::vector<cudaEvent_t> evs;
     const bool timed = st != nullptr;
     auto mark = [&]() -> int {
@@ -426,14 +460,16 @@ static int32_t run_passes(cf_lowess* h, int32_t passes, bool first_uses_rw, cf_s
     };
     int rc = CF_OK;
     bool use_rw = first_uses_rw;
+    h->timing = timed;
     for (int32_t p = 0; p < passes && rc == CF_OK; ++p) {          // :657
         if ((rc = mark()) != CF_OK) break;
         if ((rc = launch_fit(h, use_rw)) != CF_OK) break;          // :662-693
         if ((rc = mark()) != CF_OK) break;
-        if ((rc = launch_residuals(h)) != CF_OK) break;            // :695
         if (p + 1 < passes) {                                      // :696
-            if ((rc = robust_update(h)) != CF_OK) break;           // :697-713
+            if ((rc = residuals_and_robust_update(h)) != CF_OK) break;   // :695, :697-713
             use_rw = true;
+        } else {
+            if ((rc = launch_residuals(h)) != CF_OK) break;        // :695
         }
     }
     if (rc == CF_OK) rc = mark();
@@ -441,6 +477,7 @@ static int32_t run_passes(cf_lowess* h, int32_t passes, bool first_uses_rw, cf_s
         cudaError_t e = cudaStreamSynchronize(h->stream);
         if (e != cudaSuccess) rc = cuda_fail(e, "lowess passes", __FILE__, __LINE__);
     }
+    if (rc == CF_OK) rc = peer_check(h);
     if (rc == CF_OK && timed) {
         // events: [fit0 start, fit0 end, fit1 start, fit1 end, ..., final]
         float fit = 0.f, rob = 0.f, ms = 0.f;
@@ -450,7 +487,16 @@ static int32_t run_passes(cf_lowess* h, int32_t passes, bool first_uses_rw, cf_s
         }
         st->ms_fit = fit;
         st->ms_robust = rob;
+        float build = 0.f;
+        for (size_t k = 0; k + 1 < h->marks.size(); k += 2) {
+            cudaEventElapsedTime(&ms, h->marks[k], h->marks[k + 1]);
+            build += ms;
+        }
+        st->ms_tree_build = build;
     }
+    h->timing = false;
+    for (cudaEvent_t e : h->marks) cudaEventDestroy(e);
+    h->marks.clear();
     for (cudaEvent_t e : evs) cudaEventDestroy(e);
     return rc;
 }
@@ -501,6 +547,36 @@ int32_t cf_lowess_run_from_rw(cf_lowess* h, double f, const double* rw_in, int32
     if (rw_in)
         CF_CUDA(cudaMemcpyAsync(h->rw, rw_in, sizeof(double) * (size_t)h->n, cudaMemcpyHostToDevice, h->stream));
     return run_passes(h, passes, rw_in != nullptr, nullptr);
+}
+
+// One pass of the DIRECT kernel over a strided sample of its output tiles (see the header).
+int32_t cf_lowess_fit_sample(cf_lowess* h, double f, int32_t use_rw, int32_t first_tile,
+                             int32_t tile_stride, int32_t ntiles, float* ms)
+{
+    if (!h) { set_error("null handle"); return CF_INVALID_INPUT_ERROR; }
+    if (first_tile < 0 || tile_stride < 1 || ntiles < 1) {
+        set_error("bad tile sample (first %d, stride %d, count %d)", (int)first_tile, (int)tile_stride, (int)ntiles);
+        return CF_INVALID_INPUT_ERROR;
+    }
+    if (h->nseries != 1 || h->delta > 0.0) {
+        set_error("cf_lowess_fit_sample: single series with delta = 0 only");
+        return CF_INVALID_INPUT_ERROR;
+    }
+    CF_TRY(use_device(h));
+    CF_TRY(begin_stage(h, f));
+    if (h->n < 2) { set_error("n < 2"); return CF_INVALID_INPUT_ERROR; }
+    const int method = h->method;
+    h->method = CF_METHOD_DIRECT;
+    h->tile_first = first_tile; h->tile_stride = tile_stride; h->tile_count = ntiles; h->tile_ksplit = 1;
+    cudaEventRecord(h->ev[3], h->stream);
+    int rc = launch_fit(h, use_rw != 0);
+    cudaEventRecord(h->ev[4], h->stream);
+    h->tile_count = 0;
+    h->method = method;
+    if (rc != CF_OK) return rc;
+    CF_CUDA(cudaEventSynchronize(h->ev[4]));
+    if (ms) CF_CUDA(cudaEventElapsedTime(ms, h->ev[3], h->ev[4]));
+    return CF_OK;
 }
 
 int32_t cf_lowess_fetch(cf_lowess* h, double* ys, double* rw, double* res)
@@ -568,28 +644,37 @@ int32_t cf_lowess_stage_begin(cf_lowess* h, double f)
     CF_TRY(use_device(h));
     CF_TRY(begin_stage(h, f));
     if (h->n < 2) { set_error("n < 2"); return CF_INVALID_INPUT_ERROR; }
-    CF_TRY(launch_peer_spans(h));        // attached: every rank learns whose windows reach what
-    return launch_select_reset(h);
+    CF_TRY(select_prepare(h));
+    return launch_peer_spans(h);         // attached: every rank learns whose windows reach what
 }
 int32_t cf_lowess_stage_fit(cf_lowess* h, int32_t use_rw)
 {
     if (!h || !h->init) return CF_NO_DATA_DEFINED_ERROR;
     CF_TRY(use_device(h));
     CF_TRY(launch_fit(h, use_rw != 0));
-    CF_TRY(launch_residuals(h));
-    return launch_select_reset(h);
+    return launch_residuals(h);
 }
+// round 0: the B0-bit histogram of |res| over the shard (left in CF_BUF_HIST0 for the host
+// collective); round k >= 1: the k-th W-bit digit of the shard's candidates (CF_BUF_HIST)
 int32_t cf_lowess_stage_hist(cf_lowess* h, int32_t round)
 {
-    if (!h || !h->init || round < 0 || round >= kSelRounds) return CF_INVALID_INPUT_ERROR;
+    if (!h || !h->init || round < 0 || round > select_rounds(h)) return CF_INVALID_INPUT_ERROR;
     CF_TRY(use_device(h));
-    return launch_hist(h, round);
+    return round == 0 ? launch_hist0(h, false, true) : launch_cand_round(h, round, true);
 }
+// after the counters were summed over the ranks: round 0 fixes the bucket and collects the
+// shard's candidates; round k >= 1 extends the prefix (the last one forms cmad, c1, c9)
 int32_t cf_lowess_stage_pick(cf_lowess* h, int32_t round)
 {
-    if (!h || !h->init || round < 0 || round >= kSelRounds) return CF_INVALID_INPUT_ERROR;
+    if (!h || !h->init || round < 0 || round > select_rounds(h)) return CF_INVALID_INPUT_ERROR;
     CF_TRY(use_device(h));
-    return launch_pick(h, round);
+    if (round > 0) return launch_cand_pick(h, round);
+    CF_TRY(launch_pick0(h));
+    const bool attached = h->peer_attached;      // host-driven protocol: candidates stay local
+    h->peer_attached = false;
+    const int rc = launch_compact(h);
+    h->peer_attached = attached;
+    return rc;
 }
 int32_t cf_lowess_stage_weights(cf_lowess* h)
 {
@@ -615,6 +700,7 @@ void* cf_lowess_buffer(cf_lowess* h, int32_t which)
         case CF_BUF_RW: return h->rw;
         case CF_BUF_RES: return h->res;
         case CF_BUF_HIST: return h->hist;
+        case CF_BUF_HIST0: return h->hist0;
         case CF_BUF_CMAD: return &h->sel->cmad;
         default: return nullptr;
     }
@@ -646,7 +732,7 @@ static int32_t pool_acquire(cf_lowess** out)
             if (g_pool[k]->device == dev) {
                 *out = g_pool[k];
                 g_pool.erase(g_pool.begin() + (long)k);
-                (*out)->method = method_from_env();     // the stateless calls follow the environment
+                (*out)->method = g_default_method.load();
                 return CF_OK;
             }
         }
@@ -782,10 +868,11 @@ int32_t cf_lowess_smooth_batched(const double* x_sorted, const double* y, int32_
             CF_CUDA(cudaMemcpyAsync(h->ys, h->y, bytes, cudaMemcpyDeviceToDevice, h->stream));
         } else {
             bool use_rw = false;
+            CF_TRY(select_prepare(h));
             for (int32_t p = 0; p <= nsteps; ++p) {
                 CF_TRY(launch_fit(h, use_rw));
-                CF_TRY(launch_residuals(h));
-                if (p < nsteps) { CF_TRY(robust_update(h)); use_rw = true; }
+                if (p < nsteps) { CF_TRY(residuals_and_robust_update(h)); use_rw = true; }
+                else CF_TRY(launch_residuals(h));
             }
         }
         CF_CUDA(cudaMemcpyAsync(ys + off, h->ys, bytes, cudaMemcpyDeviceToHost, h->stream));

@@ -6,9 +6,20 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include <vector>
+
 #include "curvefit_cuda.h"
 
 namespace cf {
+
+// Development switches (tile variants, tree geometry sweeps) are read from the environment
+// only in builds made with -DCF_DEVELOPMENT; a release build has no environment routes.
+#ifdef CF_DEVELOPMENT
+#include <stdlib.h>
+inline const char* dev_env(const char* name) { return getenv(name); }
+#else
+inline const char* dev_env(const char*) { return nullptr; }
+#endif
 
 // ---- error plumbing ---------------------------------------------------------
 void set_error(const char* fmt, ...);
@@ -28,20 +39,40 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
     } while (0)
 
 // ---- select (median of |res|) geometry ---------------------------------------
-// 64-bit keys (bit pattern of |res|, non-negative doubles order as uint64) are
-// resolved most-significant digit first, 11 bits per round, 6 rounds (the last
-// round has 9 live bits).  Two ranks are tracked together: the reference reads
-// rw(m1) and rw(m2), m1 = 1 + n/2, m2 = n - m1 + 1
+// Keys are the bit patterns of |res| (non-negative doubles order as uint64; bit 63 is
+// always clear, so TOP = 63 informative bits) or, for cf_median, the order-preserving
+// image of the signed value (TOP = 64).  They are resolved most-significant digit first:
+// round 0 takes the top B0 bits of EVERY element (fused into the residual pass), later
+// rounds take W bits each of the CANDIDATES only (robust.cu).  Two ranks are tracked
+// together: the reference reads rw(m1) and rw(m2), m1 = 1 + n/2, m2 = n - m1 + 1
 // (src/curvefit_regression.f90:699-701).
-constexpr int kSelBits = 11;
-constexpr int kSelBins = 1 << kSelBits;
-constexpr int kSelRounds = 6;
-constexpr int kHistLen = 2 * kSelBins;  // one histogram per tracked rank
+constexpr int kSelB0Single = 15, kSelWSingle = 12;     // one series: 128 KB shared-memory histogram
+constexpr int kSelB0Batched = 11, kSelWBatched = 11;   // nseries > 1: per-series state stays small
+
+struct SelGeom { int top, b0, w, rounds; };            // rounds = number of W-bit rounds after round 0
+__host__ __device__ inline SelGeom sel_geom(bool ordered, bool batched)
+{
+    SelGeom g;
+    g.top = ordered ? 64 : 63;
+    g.b0 = batched ? kSelB0Batched : kSelB0Single;
+    g.w = batched ? kSelWBatched : kSelWSingle;
+    g.rounds = (g.top - g.b0 + g.w - 1) / g.w;
+    return g;
+}
+// round k = 1 .. rounds resolves bits [shift, shift + width)
+__host__ __device__ inline int sel_width(const SelGeom& g, int k)
+{
+    return k == 1 ? (g.top - g.b0) - g.w * (g.rounds - 1) : g.w;
+}
+__host__ __device__ inline int sel_shift(const SelGeom& g, int k) { return g.w * (g.rounds - k); }
 
 struct SelectState {
     unsigned long long prefix[2];  // resolved high bits of the two order statistics
     unsigned long long rank[2];    // remaining 0-based rank inside the prefix bucket
     double cmad, c1, c9;           // :701-703
+    unsigned int bucket[2];        // round 0: top-B0-bit bucket of each tracked rank
+    unsigned int ncand;            // keys appended to the candidate list (compact_kernel)
+    unsigned int ticket;           // CTAs of the running select kernel that have finished
 };
 
 #ifdef __CUDACC__
@@ -94,18 +125,21 @@ __device__ __forceinline__ double fit_value(double S0, double S1, double S2, dou
 // ---- peer-memory exchange (peer.cu): the robustness step's two collectives done
 // by the kernels themselves over NVLink peer stores instead of NCCL ------------
 constexpr int kMaxPeers = 8;
-struct PeerComm {                                   // one per rank, IPC-mapped by all peers
-    unsigned long long flag[2][kMaxPeers];          // [0] histogram rounds, [1] barriers: epoch per source rank
-    unsigned long long slots[2][kMaxPeers][kHistLen];  // [epoch parity][source rank] digit histograms
+struct PeerComm {                                   // one per rank, mapped by all peers
+    unsigned long long flag[2][kMaxPeers];          // [0] histogram all-reduce, [1] barriers: epoch per source rank
     int error;                                      // set when a wait timed out
     int32_t span[2];                                // this rank's element span (windows.cu), published
     int32_t peer_span[kMaxPeers][2];                // every rank's span, local copy made after the barrier
+    unsigned int cand_count[kMaxPeers];             // candidates rank r pushed into slot r of this rank's list
+    unsigned int slots[2][kMaxPeers][1 << kSelB0Single];  // [epoch parity][source rank] round-0 histograms
 };
 struct PeerPtrs {                                   // by-value kernel argument
     PeerComm* comm[kMaxPeers];
     double* rw[kMaxPeers];
     double* ys[kMaxPeers];
     double* res[kMaxPeers];
+    unsigned long long* cand[kMaxPeers];            // candidate lists (nranks slots of `block` keys)
+    unsigned long long timeout_ns;                  // device-side waits give up after this long
     int rank, nranks;
 };
 
@@ -145,9 +179,14 @@ struct cf_lowess {
     double win_f = -1.0;  // span fraction the stored windows were built for
     int32_t ns = 0;
 
-    unsigned long long* hist = nullptr;  // nseries x kHistLen counters
+    // select (robust.cu): per series the round-0 histogram, the two W-bit histograms, the state
+    unsigned int* hist0 = nullptr;       // nseries << B0 counters, zero between uses
+    unsigned int* hist = nullptr;        // nseries x 2 << W counters, zero between uses
     cf::SelectState* sel = nullptr;      // nseries states
     int32_t sel_cap = 0;
+    unsigned long long* cand = nullptr;  // candidate keys: nseries x cand_stride
+    int64_t cap_cand = 0, cand_stride = 0;
+    bool sel_attr = false;               // dynamic shared-memory opt-in done on this device
     int32_t* span = nullptr;             // nseries x {min lo9, max hi9} over the shard (windows.cu)
 
     // fit kernel: partial-moment scratch for the K-way window split, tuning knobs
@@ -156,6 +195,8 @@ struct cf_lowess {
     int sms = 0;
     int fit_variant = 0;       // env CF_FIT_VARIANT (development only)
     int ksplit_override = 0;   // env CF_FIT_KSPLIT  (development only)
+    // cf_lowess_fit_sample: launch only tiles tile_first + k * tile_stride, k < tile_count (0 = all)
+    int32_t tile_first = 0, tile_stride = 1, tile_count = 0, tile_ksplit = 1;
 
     // moment-tree evaluator (tree.cu): node storage, rebuilt every pass
     double* tree = nullptr;
@@ -176,10 +217,14 @@ struct cf_lowess {
     cf::PeerComm* comm = nullptr;
     cf::PeerPtrs peer = {};
     bool peer_attached = false;
+    bool peer_ipc = false;               // peers mapped through CUDA IPC (else: same-process peer access)
+    unsigned long long peer_timeout_ns = 60000000000ull;
     unsigned long long epoch_hist = 0, epoch_bar = 0;
 
     // counters for cf_stats
     int launches = 0, fit_launches = 0;
+    bool timing = false;                  // cf_lowess_run with stats: stage events are recorded
+    std::vector<cudaEvent_t> marks;       // pairs (start, end) around each tree rebuild
 };
 
 namespace cf {
@@ -193,15 +238,26 @@ int launch_residuals(cf_lowess* h);           // tie copy + res = y - ys on the 
 int delta_prepare(cf_lowess* h);              // delta.cu: (re)build the fitted-point list
 int launch_delta_fill(cf_lowess* h);          // delta.cu: tie copy + interpolation + res
 void delta_free(cf_lowess* h);
-int launch_select_reset(cf_lowess* h);
-int launch_hist(cf_lowess* h, int round);
-int launch_pick(cf_lowess* h, int round);
+// robust.cu: the select of the two middle order statistics of |res| and the weights
+int select_prepare(cf_lowess* h);                          // (re)allocate the candidate list
+int select_rounds(const cf_lowess* h);                     // W-bit rounds after round 0
+int launch_select(cf_lowess* h, bool fused_residuals);     // passes A-C; single GPU or peer-attached
+int launch_hist0(cf_lowess* h, bool fused, bool defer);    // pass A (defer: counters stay in hist0)
+int launch_pick0(cf_lowess* h);                            // round 0 scan on its own
+int launch_compact(cf_lowess* h);                          // pass B (+ peer exchange of the candidates)
+int launch_cand_round(cf_lowess* h, int k, bool defer);    // pass C, round k
+int launch_cand_pick(cf_lowess* h, int k);
 int launch_bisquare(cf_lowess* h);
-int select_median(cf_lowess* h, const double* d_x, int32_t n, double* d_out);   // robust.cu
+size_t select_scratch_bytes(int32_t n);
+int select_median(const double* d_x, int32_t n, double* d_out, void* scratch, cudaStream_t s, int* launches);
+int launch_peer_push(cf_lowess* h);           // peer.cu: own candidates -> every rank's list, then a barrier
 int launch_peer_barrier(cf_lowess* h);        // peer.cu: all ranks reach this point
 int launch_peer_gather(cf_lowess* h, int what);  // peer.cu: own ys/res/rw block -> every rank
 int launch_peer_spans(cf_lowess* h);          // peer.cu: publish the shard's element span, learn the peers'
 void peer_detach(cf_lowess* h);               // peer.cu
+int peer_prepare(cf_lowess* h);               // (re)allocate and clear what the peers map
+int peer_check(cf_lowess* h);                 // CF_DEVICE_ERROR when a device-side wait timed out
+int peer_clear_error(cf_lowess* h);
 
 // device radix sort of (x, index) ascending, y co-permuted; d_perm may be null
 int sort_xy_device(const double* d_x_in, const double* d_y_in, int32_t n, double* d_x_out,

@@ -44,7 +44,8 @@ struct FitParams {
     double* part;       // [tile][K][5][T] partial moments when K > 1
     Windows w;
     int32_t n, ns, begin, end, ksplit;
-    int32_t tiles;      // tiles per series
+    int32_t tiles;      // tiles per series (launched)
+    int32_t tile_first, tile_stride;   // launched tile t is tile tile_first + t * tile_stride of the shard
     const int32_t* fidx;  // delta > 0: output slot -> point (delta.cu); then begin = 0, end = #fitted
 };
 
@@ -213,7 +214,7 @@ fit_kernel(const FitParams prm_in)
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int K = prm.ksplit;
     const int tile = blockIdx.x / K, part = blockIdx.x - tile * K;
-    const int32_t tile0 = prm.begin + (int32_t)tile * T;
+    const int32_t tile0 = prm.begin + (prm.tile_first + (int32_t)tile * prm.tile_stride) * T;
     const double* __restrict__ x = prm.x;
     const double* __restrict__ y = prm.y;
     const double* __restrict__ rw = prm.rw;
@@ -457,7 +458,7 @@ fit_finalize_kernel(const FitParams prm_in)
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int K = prm.ksplit;
     const int tile = blockIdx.x;
-    const int32_t tile0 = prm.begin + (int32_t)tile * T;
+    const int32_t tile0 = prm.begin + (prm.tile_first + (int32_t)tile * prm.tile_stride) * T;
     Tile<NT, P> t;
     tile_setup<NT, P>(prm, tile0, t, rng, ts);
     if (t.jlo > t.jhi) return;
@@ -491,7 +492,17 @@ int launch_variant(cf_lowess* h, FitParams& prm, int sms)
     auto kern_cl = fit_kernel<NT, P, E, MINB, U, true>;
     CF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     CF_CUDA(cudaFuncSetAttribute(kern_cl, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const int tiles = (prm.end - prm.begin + T - 1) / T;
+    int tiles = (prm.end - prm.begin + T - 1) / T;
+    const bool sampled = h->tile_count > 0;      // cf_lowess_fit_sample: a strided subset of the tiles
+    prm.tile_first = 0;
+    prm.tile_stride = 1;
+    if (sampled) {
+        prm.tile_first = h->tile_first;
+        prm.tile_stride = h->tile_stride;
+        const int avail = tiles > h->tile_first ? (tiles - h->tile_first + h->tile_stride - 1) / h->tile_stride : 0;
+        tiles = h->tile_count < avail ? h->tile_count : avail;
+        if (tiles <= 0) return CF_OK;
+    }
     const long long all_tiles = (long long)tiles * h->nseries;
     prm.tiles = tiles;
     // K-way split of every tile's window when the tiles alone give too few waves
@@ -509,6 +520,7 @@ int launch_variant(cf_lowess* h, FitParams& prm, int sms)
     if (K > maxk) K = maxk;
     if (K > 64) K = 64;
     if (K < 1) K = 1;
+    if (sampled) K = h->tile_ksplit > 0 ? h->tile_ksplit : 1;   // the split the FULL launch would use
     // CF_FIT_VARIANT=4 (development): K <= 8 parts as one thread-block cluster that adds its
     // partial moments through DSMEM -- no scratch in HBM, no second kernel.  Measured on B200
     // at n = 1e6, ns = 5e4: 34.7 ms per pass against 32.7 ms for the scratch path (cluster

@@ -5,7 +5,7 @@
 
 namespace cf {
 
-constexpr unsigned long long kPeerTimeoutNs = 4000000000ull;   // 4 s, then PeerComm::error
+constexpr unsigned long long kPeerTimeoutDefaultNs = 60000000000ull;   // 60 s, then PeerComm::error
 
 __device__ __forceinline__ unsigned long long global_ns()
 {
@@ -23,10 +23,10 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
     asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
-__device__ __forceinline__ unsigned long long ld_relaxed_sys(const unsigned long long* p)
+__device__ __forceinline__ unsigned int ld_relaxed_sys_u32(const unsigned int* p)
 {
-    unsigned long long v;
-    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    unsigned int v;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
 
@@ -42,7 +42,7 @@ __device__ __forceinline__ void peer_signal_wait(const PeerPtrs& pp, int channel
         const unsigned long long* mine = &pp.comm[pp.rank]->flag[channel][p];
         const unsigned long long t0 = global_ns();
         while (ld_acquire_sys(mine) < epoch) {
-            if (global_ns() - t0 > kPeerTimeoutNs) {
+            if (global_ns() - t0 > pp.timeout_ns) {
                 pp.comm[pp.rank]->error = 1;
                 break;
             }
@@ -51,14 +51,14 @@ __device__ __forceinline__ void peer_signal_wait(const PeerPtrs& pp, int channel
     }
 }
 
-// All-reduce (sum) of `hist[0..kHistLen)` over the ranks, result in place on every
-// rank.  Called by ALL threads of a single CTA.
-__device__ __forceinline__ void peer_hist_allreduce(const PeerPtrs& pp, unsigned long long* hist,
+// All-reduce (sum) of the `len` <= 2^kSelB0Single counters hist[] over the ranks, result in place
+// on every rank.  Called by ALL threads of a single CTA.
+__device__ __forceinline__ void peer_hist_allreduce(const PeerPtrs& pp, unsigned int* hist, int len,
                                                     unsigned long long epoch)
 {
     const int par = (int)(epoch & 1ull);
-    for (int k = threadIdx.x; k < kHistLen; k += blockDim.x) {
-        const unsigned long long v = hist[k];
+    for (int k = threadIdx.x; k < len; k += blockDim.x) {
+        const unsigned int v = __ldcg(hist + k);
 #pragma unroll
         for (int p = 0; p < kMaxPeers; ++p)
             if (p < pp.nranks) pp.comm[p]->slots[par][pp.rank][k] = v;
@@ -68,11 +68,12 @@ __device__ __forceinline__ void peer_hist_allreduce(const PeerPtrs& pp, unsigned
     peer_signal_wait(pp, 0, epoch);
     __syncthreads();
     const PeerComm* own = pp.comm[pp.rank];
-    for (int k = threadIdx.x; k < kHistLen; k += blockDim.x) {
-        unsigned long long s = 0ull;
-        for (int p = 0; p < pp.nranks; ++p) s += ld_relaxed_sys(&own->slots[par][p][k]);
+    for (int k = threadIdx.x; k < len; k += blockDim.x) {
+        unsigned int s = 0u;
+        for (int p = 0; p < pp.nranks; ++p) s += ld_relaxed_sys_u32(&own->slots[par][p][k]);
         hist[k] = s;
     }
+    __threadfence();
     __syncthreads();
 }
 

@@ -133,31 +133,40 @@ int32_t cf_median(const double* x, int32_t n, double* z)
 {
     if (n < 0 || !z || (n > 0 && !x)) { set_error("Input array sizes must match."); return CF_ARRAY_SIZE_ERROR; }
     if (n == 0) { *z = 0.0; return CF_OK; }                      // :280-283
-    cf_lowess* h = nullptr;
-    CF_TRY(cf_lowess_create(&h, -1, nullptr));                   // select state + stream
-    double* dx = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        set_error("no CUDA device available; libcurvefit_cuda has no CPU fallback");
+        return CF_DEVICE_ERROR;
+    }
+    // one allocation: data | result | select scratch
     const size_t bytes = sizeof(double) * (size_t)n;
-    cudaError_t e = cudaMalloc(&dx, bytes + sizeof(double));
-    if (e == cudaSuccess) e = cudaMemcpyAsync(dx, x, bytes, cudaMemcpyHostToDevice, h->stream);
-    int rc = e == cudaSuccess ? select_median(h, dx, n, dx + n)
+    unsigned char* d = nullptr;
+    cudaError_t e = cudaMalloc(&d, bytes + 256 + select_scratch_bytes(n));
+    if (e != cudaSuccess) return cuda_fail(e, "cf_median alloc", __FILE__, __LINE__);
+    double* dx = reinterpret_cast<double*>(d);
+    double* dz = reinterpret_cast<double*>(d + bytes);
+    e = cudaMemcpyAsync(dx, x, bytes, cudaMemcpyHostToDevice, cudaStreamPerThread);
+    int rc = e == cudaSuccess ? select_median(dx, n, dz, d + bytes + 256, cudaStreamPerThread, nullptr)
                               : cuda_fail(e, "cf_median upload", __FILE__, __LINE__);
     if (rc == CF_OK) {
-        e = cudaMemcpyAsync(z, dx + n, sizeof(double), cudaMemcpyDeviceToHost, h->stream);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+        e = cudaMemcpyAsync(z, dz, sizeof(double), cudaMemcpyDeviceToHost, cudaStreamPerThread);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(cudaStreamPerThread);
         if (e != cudaSuccess) rc = cuda_fail(e, "cf_median", __FILE__, __LINE__);
     }
-    cudaFree(dx);
-    cf_lowess_destroy(h);
+    cudaFree(d);
     return rc;
 }
 
+// Asynchronous on `stream` (a cudaStream_t; NULL = the legacy default stream, like
+// cf_moving_average_device): the scratch is allocated and freed in stream order.
 int32_t cf_median_device(const void* d_x, int32_t n, void* d_z, void* stream)
 {
     if (n < 1 || !d_x || !d_z) { set_error("Input array sizes must match."); return CF_ARRAY_SIZE_ERROR; }
-    cf_lowess* h = nullptr;
-    CF_TRY(cf_lowess_create(&h, -1, stream));
-    int rc = select_median(h, static_cast<const double*>(d_x), n, static_cast<double*>(d_z));
-    cf_lowess_destroy(h);                                        // synchronises the stream
+    cudaStream_t s = (cudaStream_t)stream;
+    void* scratch = nullptr;
+    CF_CUDA(cudaMallocAsync(&scratch, select_scratch_bytes(n), s));
+    const int rc = select_median(static_cast<const double*>(d_x), n, static_cast<double*>(d_z), scratch, s, nullptr);
+    cudaFreeAsync(scratch, s);
     return rc;
 }
 

@@ -848,7 +848,7 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
             for (int g = 1; g <= G; ++g) bits[g] = T / G + (g <= T % G ? 1 : 0);
             for (int g = 1; g <= G; ++g) if (bits[g] > 9) bits[g] = 9;
         }
-        if (const char* v = getenv("CF_TREE_BITS")) {        // development: "8,8" etc.
+        if (const char* v = dev_env("CF_TREE_BITS")) {        // development: "8,8" etc.
             G = 0;
             while (*v && G < kMaxGroups) {
                 bits[++G] = atoi(v);
@@ -878,10 +878,18 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
     }
     prm.nodes = h->tree;
     prm.span = h->span;
+    auto mark = [&]() {
+        if (!h->timing) return;
+        cudaEvent_t e;
+        if (cudaEventCreate(&e) != cudaSuccess) return;
+        cudaEventRecord(e, h->stream);
+        h->marks.push_back(e);
+    };
+    mark();
 
     // the part of the tree inside each block of 2^cb leaves in one launch (with the level-1
     // chain when its blocks are those); CF_TREE_FUSED=0: one launch per level as before
-    static const bool fused = !(getenv("CF_TREE_FUSED") && atoi(getenv("CF_TREE_FUSED")) == 0);
+    static const bool fused = !(dev_env("CF_TREE_FUSED") && atoi(dev_env("CF_TREE_FUSED")) == 0);
     int level = 1;
     int g0 = 1;
     if (fused) {
@@ -889,7 +897,7 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
         int cb = chain ? prm.cbits[1] : 8;
         if (cb > L - 1) cb = L - 1;
         // few blocks: 128 threads per block (shortest critical path); many: one warp per block
-        static const int bt_env = getenv("CF_TREE_BLOCK") ? atoi(getenv("CF_TREE_BLOCK")) : 0;
+        static const int bt_env = dev_env("CF_TREE_BLOCK") ? atoi(dev_env("CF_TREE_BLOCK")) : 0;
         const int64_t leaves = (int64_t)prm.cnt[0] * h->nseries;
         const int bt = bt_env ? bt_env : (leaves < (1 << 20) ? 128 : 32);
         const dim3 bg((prm.cnt[0] + (1 << cb) - 1) >> cb, h->nseries);
@@ -927,11 +935,12 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
         CF_CUDA(cudaGetLastError());
         h->launches++;
     }
+    mark();
     const int cntp = prm.end - prm.begin;
     // 7 CTAs of 128 threads per SM (72 registers) + L1 prefetch of the next node; the
     // others are kept for measurement (B200, n = 1e8 smooth: 5 CTAs 143.2 ms, 6: 128.6,
     // 7: 125.7, 7 + prefetch 125.3)
-    static const int variant = getenv("CF_TREE_EVAL") ? atoi(getenv("CF_TREE_EVAL")) : 7;
+    static const int variant = dev_env("CF_TREE_EVAL") ? atoi(dev_env("CF_TREE_EVAL")) : 7;
     const dim3 eg((cntp + 127) / 128, h->nseries);
     switch (variant) {
     case 5:  tree_eval_kernel<128, 5, 0><<<eg, 128, 0, h->stream>>>(prm); break;

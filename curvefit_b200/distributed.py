@@ -3,17 +3,20 @@
 One process per GPU (torchrun); every rank holds the whole sorted x, y (16 B
 per point) and the whole robustness-weight vector, fits only its own block
 [begin, end) of output points, and per robustness iteration exchanges
-  * the |res| digit histograms (6 rounds x 4096 uint64 counters, all-reduce)
-    -> every rank resolves the same two order statistics, hence the same cmad
-    (src/curvefit_regression.f90:697-703 -- the reference's full sort);
+  * what the exact select of the two middle order statistics of |res| needs
+    (src/curvefit_regression.f90:697-703 -- the reference's full sort): the
+    digit histograms of the radix select (round 0: 2^15 counters over every
+    residual; later rounds: 2 x 2^12 counters over the few candidates), summed
+    over the ranks -> every rank resolves the same cmad;
   * its block of new robustness weights (all-gather) -- the superset of the
     (ns-1)-point halo the neighbours need for :551.
-Two transports: "p2p" (default on GPUs) -- the kernels do both exchanges
-themselves through NVLink peer memory (csrc/peer.cu: histogram all-reduce fused
-into the select scan, weights stored straight into every rank's vector, device
+Two transports: "p2p" (default on GPUs) -- the kernels do the exchanges
+themselves through NVLink peer memory inside ONE cf_lowess_run call per rank
+(csrc/peer.cu: round-0 histogram all-reduce fused into the residual pass's scan,
+candidate keys and halo weights stored straight into every rank's memory, device
 barriers; torch.distributed only carries the CUDA IPC handles once) -- and "nccl"
-(torch.distributed collectives between the stages; also what the gloo CPU tests
-exercise).  The device stages are libcurvefit_cuda's cf_lowess_stage_* entry points.  Per-point
+(torch.distributed collectives between the device stages -- the baseline, and
+what the gloo CPU tests exercise).  The device stages are libcurvefit_cuda's cf_lowess_stage_* entry points.  Per-point
 sums never cross ranks, so ys is bit-identical for any number of ranks.
 """
 from __future__ import annotations
@@ -76,7 +79,8 @@ class DeviceStages:
         self.begin, self.end, self.block = b.value, e.value, blk.value
         dev = torch.device("cuda", torch.cuda.current_device())
         buf = lambda which: self.lib.cf_lowess_buffer(self.h, which)
-        self.hist = torch.as_tensor(_DevArray(buf(_lib.CF_BUF_HIST), self.lib.cf_lowess_hist_len(), "<i8"), device=dev)
+        self.hist0 = torch.as_tensor(_DevArray(buf(_lib.CF_BUF_HIST0), self.lib.cf_lowess_hist0_len(), "<i4"), device=dev)
+        self.hist = torch.as_tensor(_DevArray(buf(_lib.CF_BUF_HIST), self.lib.cf_lowess_hist_len(), "<i4"), device=dev)
         self.rw = torch.as_tensor(_DevArray(buf(_lib.CF_BUF_RW), nranks * self.block, "<f8"), device=dev)
         self.ys = torch.as_tensor(_DevArray(buf(_lib.CF_BUF_YS), self.n, "<f8"), device=dev)
         self.res = torch.as_tensor(_DevArray(buf(_lib.CF_BUF_RES), self.n, "<f8"), device=dev)
@@ -155,8 +159,19 @@ class DeviceStages:
     def pick_round(self, r: int) -> None:
         self._check(self.lib.cf_lowess_stage_pick(self.h, r))
 
+    def hist_view(self, r: int):
+        """The counters round r's collective must sum over the ranks."""
+        return self.hist0 if r == 0 else self.hist
+
     def weights(self) -> None:
         self._check(self.lib.cf_lowess_stage_weights(self.h))
+
+    def run_fused(self, f: float, nsteps: int):
+        """p2p transport: the whole smooth in one collective C call (cf_lowess_run on an
+        attached handle); returns its cf_stats, raises when a peer wait timed out."""
+        st = _lib.cf_stats()
+        self._check(self.lib.cf_lowess_run(self.h, float(f), int(nsteps), C.byref(st)))
+        return st
 
     def sync(self) -> None:
         self._check(self.lib.cf_lowess_sync(self.h))
@@ -174,7 +189,13 @@ class ShardedLowess:
 
     def run(self, f: float, nsteps: int = 2, gather: bool = True, with_rw: bool = False):
         s = self.s
-        multi = s.nranks > 1 and not getattr(s, "p2p", False)   # p2p: the kernels exchange
+        self.last_stats = None
+        if getattr(s, "p2p", False):
+            # the kernels exchange; a timed-out peer wait makes cf_lowess_run fail on the rank
+            # that saw it -- the other ranks learn it from check_all()
+            self.last_stats = s.run_fused(f, nsteps)
+            return self.gather_results(with_rw) if gather else None
+        multi = s.nranks > 1
         s.begin_run(f)
         for p in range(nsteps + 1):                           # :657
             s.fit_pass(p > 0)                                 # :662-695 on the block
@@ -183,7 +204,7 @@ class ShardedLowess:
             for r in range(s.rounds):                         # :697-703 as a radix select
                 s.hist_round(r)
                 if multi:
-                    dist.all_reduce(s.hist, op=dist.ReduceOp.SUM, group=self.group)
+                    dist.all_reduce(s.hist_view(r), op=dist.ReduceOp.SUM, group=self.group)
                     self.collectives += 1
                 s.pick_round(r)
             s.weights()                                       # :704-713 on the block
@@ -194,6 +215,17 @@ class ShardedLowess:
         if not gather:
             return None
         return self.gather_results(with_rw)
+
+    def check_all(self) -> None:
+        """Collective: raises on EVERY rank when any rank's device-side peer wait timed out
+        (its results would be built on missing histograms or halo weights)."""
+        s = self.s
+        if not getattr(s, "p2p", False):
+            return
+        bad = torch.tensor([1 if s.peer_error() else 0], device=s.ys.device)
+        dist.all_reduce(bad, op=dist.ReduceOp.MAX, group=self.group)
+        if int(bad.item()) != 0:
+            raise RuntimeError("a peer-memory wait timed out on some rank: results are invalid")
 
     def smooth_host(self, x: np.ndarray, y: np.ndarray, f: float, nsteps: int = 2, out=None):
         """smooth() with HOST buffers on every call: each rank uploads the (sorted) series,

@@ -39,6 +39,14 @@ def _ip(a: Optional[np.ndarray]):
     return None if a is None else a.ctypes.data_as(_lib.c_ip)
 
 
+def set_default_method(method) -> None:
+    """Evaluator of handles created from now on and of the stateless calls (process-wide)."""
+    code = _METHODS[method] if isinstance(method, str) else int(method)
+    rc = _lib.load().cf_set_default_method(code)
+    if rc != 0:
+        raise RuntimeError(f"cf_set_default_method failed ({rc}): {_lib.last_error()}")
+
+
 def moving_average(x: np.ndarray, npts: int, err: Optional[errors] = None) -> None:
     """moving_average_1 (src/curvefit_regression.f90:427-478): smooths the signal x IN
     PLACE with an npts-sample moving average (zeros before the start of the signal,
@@ -232,6 +240,30 @@ class lowess_smoothing:
         if rc != 0:
             raise RuntimeError(f"cf_lowess_fetch failed ({rc}): {_lib.last_error()}")
         return ys, rwo, res
+
+    def fit_sample(self, f: float, use_rw: bool, first_tile: int, tile_stride: int, ntiles: int,
+                   tile: int = 512):
+        """One pass of the DIRECT kernel over the strided tile sample (cf_lowess_fit_sample).
+        Returns (ms of the launch, 0-based indices of the sampled points, ys at them)."""
+        if not self.m_init:
+            raise RuntimeError("No data has been defined.")
+        n = self.m_x.size
+        ms = C.c_float(0.0)
+        rc = self._lib.cf_lowess_fit_sample(self._h, float(f), 1 if use_rw else 0, int(first_tile),
+                                            int(tile_stride), int(ntiles), C.byref(ms))
+        if rc != 0:
+            raise RuntimeError(f"cf_lowess_fit_sample failed ({rc}): {_lib.last_error()}")
+        b, e = C.c_int32(), C.c_int32()
+        self._lib.cf_lowess_shard(self._h, C.byref(b), C.byref(e), None)   # tiles count from the shard's start
+        tiles_all = -(-(e.value - b.value) // tile)
+        t = np.arange(first_tile, tiles_all, tile_stride, dtype=np.int64)[:ntiles]
+        idx = (b.value + t[:, None] * tile + np.arange(tile)[None, :]).ravel()
+        idx = idx[idx < e.value]
+        ys = np.empty(n)
+        rc = self._lib.cf_lowess_fetch(self._h, _dp(ys), None, None)
+        if rc != 0:
+            raise RuntimeError(f"cf_lowess_fetch failed ({rc}): {_lib.last_error()}")
+        return float(ms.value), idx, ys[idx]
 
     # -- accessors (:876-939) ------------------------------------------------------------
     def get_count(self) -> int:

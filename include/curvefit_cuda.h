@@ -112,6 +112,8 @@ CF_API int32_t cf_moving_average_device(const void* d_x, void* d_out, int32_t n,
  * n = 0 (:280-283).  x is not modified; a caller that wants the reference's
  * srt = .true. side effect (x sorted on return) calls cf_sort as well. */
 CF_API int32_t cf_median(const double* x, int32_t n, double* z);
+/* Same on device memory, asynchronous on `stream` (a cudaStream_t; NULL = the legacy
+ * default stream, as for cf_moving_average_device); scratch is allocated in stream order. */
 CF_API int32_t cf_median_device(const void* d_x, int32_t n, void* d_z, void* stream);
 
 /* sort(x, .true.) (LINALG linalg_sorting.f90:12-35 -> DLASRT 'I'): ascending values
@@ -134,6 +136,8 @@ typedef struct cf_stats {
     int32_t ns;          /* span used                                         */
     int32_t passes;      /* nsteps + 1                                        */
     double cmad_last;    /* cmad of the last robustness iteration (:701)      */
+    float ms_tree_build; /* part of ms_fit: per-pass rebuild of the moment tree */
+    float reserved;
 } cf_stats;
 
 /* device < 0: current device.  stream: a cudaStream_t (as void*) or NULL for a
@@ -171,14 +175,16 @@ CF_API int32_t cf_lowess_shard(const cf_lowess* h, int32_t* begin, int32_t* end,
  *                    from per-block power moments, equal to rounding (<= 1e-12
  *                    relative measured; contract 1e-10);
  *  CF_METHOD_AUTO    tree when ns >= 1024, else direct.
- * Default: CF_METHOD_DIRECT, or the environment variable CF_LOWESS_METHOD
- * (direct | tree | auto), read at cf_lowess_create and by every stateless call
- * (cf_lowess_smooth, cf_lowess_smooth_delta). */
+ * Default: CF_METHOD_DIRECT.  cf_set_default_method changes, process-wide, the method of
+ * handles created afterwards and of the stateless calls (cf_lowess_smooth, _delta,
+ * _batched, _multi); there is no environment route. */
 #define CF_METHOD_DIRECT 0
 #define CF_METHOD_TREE 1
 #define CF_METHOD_AUTO 2
 CF_API int32_t cf_lowess_set_method(cf_lowess* h, int32_t method);
 CF_API int32_t cf_lowess_method(const cf_lowess* h);
+CF_API int32_t cf_set_default_method(int32_t method);
+CF_API int32_t cf_default_method(void);
 
 /* delta of later runs on this handle (default 0 = every distinct x is fitted).
  * delta > 0: single series, one GPU (no batched / sharded handles). */
@@ -202,6 +208,19 @@ CF_API int32_t cf_lowess_run(cf_lowess* h, double f, int32_t nsteps, cf_stats* s
  * weights (host, length n; NULL = first pass without weights). */
 CF_API int32_t cf_lowess_run_from_rw(cf_lowess* h, double f, const double* rw_in,
                                      int32_t passes);
+
+/* ONE lowest() pass (:513-586 over the points of :662-673) of the DIRECT kernel on a
+ * strided sample of its 512-point output tiles: tiles first_tile, first_tile +
+ * tile_stride, ... (ntiles of them, clipped to the handle's shard), each evaluated
+ * exactly as in a full pass (whole window, no window split -- the geometry a full
+ * pass uses once the tiles alone fill the GPU).  use_rw = 0: the unweighted first
+ * pass (:671 userw = .false.); 1: with the handle's current robustness weights.  ys
+ * is written at the sampled points only; *ms (may be NULL) receives the CUDA-event
+ * time of the launch.  This is how a direct pass at n = 1e8, ns = 5e6 -- 5.5 minutes
+ * in full -- is measured and parity-checked in seconds.  Single series, delta = 0. */
+CF_API int32_t cf_lowess_fit_sample(cf_lowess* h, double f, int32_t use_rw,
+                                    int32_t first_tile, int32_t tile_stride,
+                                    int32_t ntiles, float* ms);
 
 /* Copy results to host buffers (each may be NULL): last ys, m_weights,
  * m_residuals (what get_residuals returns, :928-939). */
@@ -229,6 +248,12 @@ CF_API int32_t cf_lowess_windows(cf_lowess* h, double f,
  * ---------------------------------------------------------------------- */
 CF_API int32_t cf_lowess_stage_begin(cf_lowess* h, double f);        /* windows          */
 CF_API int32_t cf_lowess_stage_fit(cf_lowess* h, int32_t use_rw);    /* fit + res, shard */
+/* The select of the two middle order statistics of |res| (:697-703), one radix digit per
+ * round, most significant first: round 0 counts the top 15 key bits of every residual of
+ * the shard into CF_BUF_HIST0; rounds 1 .. cf_lowess_select_rounds() - 1 count 12 more
+ * bits each, of the shard's CANDIDATES only (the keys of the bucket round 0 chose), into
+ * CF_BUF_HIST.  The host runtime sums the counters over the ranks (integer all-reduce)
+ * between _stage_hist and _stage_pick of the same round; the last pick forms cmad. */
 CF_API int32_t cf_lowess_stage_hist(cf_lowess* h, int32_t round);    /* |res| digit hist */
 CF_API int32_t cf_lowess_stage_pick(cf_lowess* h, int32_t round);    /* scan (post-sum)  */
 CF_API int32_t cf_lowess_stage_weights(cf_lowess* h);                /* bisquare, shard  */
@@ -250,12 +275,24 @@ CF_API int32_t cf_lowess_sync(cf_lowess* h);
  *   2. the host runtime all-gathers them (rank-major) and every rank calls
  *      cf_lowess_peer_attach, then synchronises with the others once;
  *   3. all ranks issue the same sequence of stage calls.
- * A rank that never arrives does not hang the others: waits give up after 4 s
- * and cf_lowess_peer_error reports it.  init / set_shard detach.  At most 8 ranks.
+ * A rank that never arrives does not hang the others: waits give up after
+ * cf_lowess_peer_set_timeout seconds (default 60), cf_lowess_run and
+ * cf_lowess_stage_gather then return CF_DEVICE_ERROR (cf_lowess_peer_error reads the same
+ * flag).  cf_lowess_set_shard with a different layout detaches; cf_lowess_init on an
+ * attached handle keeps the mapping when the buffers stay in place (same n) and FAILS with
+ * CF_INVALID_INPUT_ERROR when it would have to reallocate them -- detach on all ranks
+ * first (a peer may still be storing into the old buffers).  At most 8 ranks.
  * ---------------------------------------------------------------------- */
 CF_API int32_t cf_lowess_peer_handle_bytes(void);
 CF_API int32_t cf_lowess_peer_export(cf_lowess* h, void* handles_out);
 CF_API int32_t cf_lowess_peer_attach(cf_lowess* h, const void* all_handles, int32_t nranks);
+/* Same-process variant: hs[r] holds shard r of nranks (one handle per device, all created
+ * by this process); peers are reached through cudaDeviceEnablePeerAccess.  This is what
+ * cf_lowess_smooth_multi uses. */
+CF_API int32_t cf_lowess_peer_attach_local(cf_lowess* const* hs, int32_t nranks);
+/* Device-side waits give up after `seconds` (default 60) and the run returns
+ * CF_DEVICE_ERROR.  Set before attaching or at any time after. */
+CF_API int32_t cf_lowess_peer_set_timeout(cf_lowess* h, double seconds);
 CF_API int32_t cf_lowess_peer_detach(cf_lowess* h);
 CF_API int32_t cf_lowess_peer_attached(const cf_lowess* h);
 CF_API int32_t cf_lowess_peer_error(cf_lowess* h, int32_t* flag);
@@ -273,10 +310,12 @@ CF_API int32_t cf_lowess_stage_gather(cf_lowess* h, int32_t what);
 #define CF_BUF_YS 2
 #define CF_BUF_RW 3      /* length = nranks * block (padded for all-gather)  */
 #define CF_BUF_RES 4
-#define CF_BUF_HIST 5    /* uint64 counters, cf_lowess_hist_len() of them     */
+#define CF_BUF_HIST 5    /* uint32 counters, cf_lowess_hist_len() of them     */
 #define CF_BUF_CMAD 6    /* double[3]: cmad, c1, c9 of the last iteration     */
+#define CF_BUF_HIST0 7   /* uint32 counters, cf_lowess_hist0_len() of them    */
 CF_API void* cf_lowess_buffer(cf_lowess* h, int32_t which);
 CF_API int32_t cf_lowess_hist_len(void);
+CF_API int32_t cf_lowess_hist0_len(void);
 
 /* FP64 pipe peak microbenchmark (independent DFMA chains on every SM):
  * returns measured TFLOP/s (FMA = 2 flop) over `ms_target` milliseconds. */

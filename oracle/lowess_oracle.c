@@ -458,6 +458,28 @@ ORACLE_API int cf_oracle_ls_smooth(const double *m_x, const double *m_y, int n,
                             m_residuals, NULL, NULL, NULL, NULL);
 }
 
+/* The robustness step on its own (:697-713): |res| -> full ascending sort -> cmad ->
+ * bisquare weights; single-threaded like the reference.  bench.py times it so that the
+ * extrapolated CPU smooth() includes the sort. */
+ORACLE_API double cf_oracle_robust_weights(const double *res0, double *rw0, int n)
+{
+    return robust_weights_1b(res0 - 1, rw0 - 1, n);
+}
+
+/* Number of OpenMP threads of the multi-threaded entry points from now on (they default
+ * to OMP_NUM_THREADS, which launchers such as torchrun set to 1).  Returns the value in
+ * effect. */
+ORACLE_API int cf_oracle_set_threads(int nthreads)
+{
+#ifdef _OPENMP
+    if (nthreads > 0) omp_set_num_threads(nthreads);
+    return omp_get_max_threads();
+#else
+    (void)nthreads;
+    return 1;
+#endif
+}
+
 ORACLE_API int cf_oracle_max_threads(void)
 {
 #ifdef _OPENMP

@@ -64,6 +64,10 @@ def lib() -> C.CDLL:
         L.cf_oracle_moving_average.restype = C.c_int
         L.cf_oracle_median.argtypes = [_dp, C.c_int, C.c_int]
         L.cf_oracle_median.restype = C.c_double
+        L.cf_oracle_set_threads.argtypes = [C.c_int]
+        L.cf_oracle_set_threads.restype = C.c_int
+        L.cf_oracle_robust_weights.argtypes = [_dp, _dp, C.c_int]
+        L.cf_oracle_robust_weights.restype = C.c_double
         L.cf_oracle_max_threads.argtypes = []
         L.cf_oracle_max_threads.restype = C.c_int
         _lib = L
@@ -166,6 +170,28 @@ def ls_init(x, y, srt=True):
 
 def max_threads() -> int:
     return int(lib().cf_oracle_max_threads())
+
+
+def set_threads(nthreads: int) -> int:
+    """Threads of lowest_at / lowess_mt from now on (overrides OMP_NUM_THREADS, which
+    torchrun exports as 1).  Returns the value in effect."""
+    return int(lib().cf_oracle_set_threads(int(nthreads)))
+
+
+def host_cores() -> int:
+    """Cores this process may run on."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def robust_weights(res):
+    """:697-713 on its own: (cmad, rw) from the residuals, single-threaded full sort."""
+    res = _f64(res)
+    rw = np.zeros_like(res)
+    c = lib().cf_oracle_robust_weights(_d(res), _d(rw), res.size)
+    return float(c), rw
 
 
 def moving_average(x, npts):

@@ -16,7 +16,10 @@ import torch.multiprocessing as mp
 from curvefit_b200.distributed import ShardedLowess, partition
 from tests import cases
 
-BITS, ROUNDS = 11, 6
+# the select geometry of csrc/common.cuh (one series): keys of 63 informative bits, round 0
+# takes the top 15 of every residual, rounds 1..4 take 12 bits each of the candidates only
+TOP, B0, W = 63, 15, 12
+ROUNDS = 1 + (TOP - B0 + W - 1) // W
 
 
 class NumpyStages:
@@ -30,7 +33,8 @@ class NumpyStages:
         self.rank, self.nranks = rank, nranks
         self.block, parts = partition(self.n, nranks)
         self.begin, self.end = parts[rank]
-        self.hist = torch.zeros(2 << BITS, dtype=torch.int64)
+        self.hist0 = torch.zeros(1 << B0, dtype=torch.int32)
+        self.hist = torch.zeros(2 << W, dtype=torch.int32)
         self.rw = torch.zeros(nranks * self.block, dtype=torch.float64)
         self.ys = torch.zeros(self.n, dtype=torch.float64)
         self.res = torch.zeros(self.n, dtype=torch.float64)
@@ -38,6 +42,7 @@ class NumpyStages:
         self.rounds = ROUNDS
         self.prefix = [0, 0]
         self.krank = [0, 0]
+        self.cand = np.zeros(0, np.uint64)
 
     def begin_run(self, f):
         self.f = f
@@ -49,35 +54,51 @@ class NumpyStages:
             t = self.o.lowest_at(self.x, self.y, self.f, idx, rw)
             self.ys.numpy()[self.begin:self.end] = t["ys"]
             self.res.numpy()[self.begin:self.end] = self.y[self.begin:self.end] - t["ys"]
-        self.prefix = [0, 0]
-        self.krank = [(self.n - 1) // 2, self.n // 2]
-        self.hist.zero_()
+
+    def hist_view(self, r):
+        return self.hist0 if r == 0 else self.hist
 
     @staticmethod
-    def _geom(r):
-        s = 64 - BITS * (r + 1)
-        return max(s, 0), (BITS if s >= 0 else BITS + s)
+    def _geom(k):
+        """(shift, width) of round k >= 1."""
+        rounds = ROUNDS - 1
+        width = (TOP - B0) - W * (rounds - 1) if k == 1 else W
+        return W * (rounds - k), width
 
     def hist_round(self, r):
+        if r == 0:
+            keys = np.abs(self.res.numpy()[self.begin:self.end]).view(np.uint64)
+            self.hist0.numpy()[:] = np.bincount((keys >> np.uint64(TOP - B0)).astype(np.int64), minlength=1 << B0)
+            return
         shift, width = self._geom(r)
-        keys = np.abs(self.res.numpy()[self.begin:self.end]).view(np.uint64)
-        hs = shift + width
-        hi = (keys >> np.uint64(hs)) if hs < 64 else np.zeros_like(keys)
-        d = ((keys >> np.uint64(shift)) & np.uint64((1 << width) - 1)).astype(np.int64)
+        hi = self.cand >> np.uint64(shift + width)
+        d = ((self.cand >> np.uint64(shift)) & np.uint64((1 << width) - 1)).astype(np.int64)
         h = self.hist.numpy()
-        for t in range(2):
-            sel = d[hi == np.uint64(self.prefix[t])]
-            h[t << BITS:(t + 1) << BITS] += np.bincount(sel, minlength=1 << BITS)
+        h[:] = 0
+        same = self.prefix[0] == self.prefix[1]
+        for t in range(1 if same else 2):
+            h[t << W:(t + 1) << W] = np.bincount(d[hi == np.uint64(self.prefix[t])], minlength=1 << W)
 
     def pick_round(self, r):
+        if r == 0:
+            c = np.cumsum(self.hist0.numpy().astype(np.int64))
+            for t, k in enumerate([(self.n - 1) // 2, self.n // 2]):
+                b = int(np.searchsorted(c, k, side="right"))
+                self.krank[t] = k - (int(c[b - 1]) if b > 0 else 0)
+                self.prefix[t] = b
+            keys = np.abs(self.res.numpy()[self.begin:self.end]).view(np.uint64)
+            top = keys >> np.uint64(TOP - B0)
+            self.cand = keys[(top == np.uint64(self.prefix[0])) | (top == np.uint64(self.prefix[1]))]
+            return
         _, width = self._geom(r)
-        h = self.hist.numpy()
+        h = self.hist.numpy().astype(np.int64)
+        same = self.prefix[0] == self.prefix[1]
         for t in range(2):
-            c = np.cumsum(h[t << BITS:(t + 1) << BITS])
+            src = h[:1 << W] if (same or t == 0) else h[1 << W:]
+            c = np.cumsum(src)
             b = int(np.searchsorted(c, self.krank[t], side="right"))
             self.krank[t] -= int(c[b - 1]) if b > 0 else 0
             self.prefix[t] = (self.prefix[t] << width) | b
-        self.hist.zero_()
         if r == ROUNDS - 1:
             lo, hi = (np.array(self.prefix, dtype=np.uint64).view(np.float64))
             cmad = 3.0 * (hi + lo)

@@ -101,6 +101,36 @@ def test_c4_full_tree_and_linear_property(cf, oracle):
     _teacher(fit, oracle, x, y, f, rw_in, ys0, 36)
 
 
+def test_c4_direct_kernel_sampled_pass(cf, oracle):
+    """The DIRECT kernel at the headline geometry n = 1e8, ns = 5e6 (a full pass is 5.5 min):
+    one weighted pass over a strided sample of one wave of 512-point tiles plus the first and
+    the last tile, each evaluated exactly as in a full pass (K = 1, 19 532 staged chunks per
+    tile), against the oracle's lowest() fed with the same robustness weights, and against the
+    moment tree's pass from the same weights."""
+    n, f = 100_000_000, 0.05
+    x = datagen.grid_x(n)
+    y = datagen.noisy_y(x)
+    fit = cf.lowess_smoothing()
+    fit.set_method("tree")
+    fit.initialize(x, y, srt=False)
+    fit.smooth(f, nsteps=1)                       # robustness weights of one iteration
+    rw_in = fit.m_weights.copy()
+    ys_tree, _, _ = fit.run_from_rw(f, rw_in, passes=1)
+    tiles = -(-n // 512)
+    stride = tiles // 592
+    ms, idx, ysd = fit.fit_sample(f, True, stride // 2, stride, 592)
+    assert idx.size == 592 * 512 and ms > 0
+    ms2, idx2, ysd2 = fit.fit_sample(f, True, 0, tiles - 1, 2)      # both ends of the series
+    idx = np.concatenate([idx, idx2]); ysd = np.concatenate([ysd, ysd2])
+    assert np.all(np.isfinite(ysd))
+    assert cases.close(ysd, ys_tree[idx], TOL)[0]
+    pick = np.unique(np.concatenate([np.arange(0, 3), np.arange(idx.size - 3, idx.size),
+                                     np.linspace(0, idx.size - 1, 26).astype(np.int64)]))
+    t = oracle.lowest_at(x, y, f, idx[pick].astype(np.int32), rw_in)
+    ok, d, nref = cases.close_or_exact(ysd[pick], t["ys"], x, y, rw_in, f, TOL, idx=idx[pick].astype(np.int32))
+    assert ok and nref == 0, (d, nref)
+
+
 def test_c5_full_wide_span_both_evaluators(cf, oracle):
     """BASELINE configs[4]: n = 2e6, f = 0.8, 5 robustness iterations.  The whole smooth runs
     on the tree; one weighted pass of the direct kernel (2 s) must agree with it and with

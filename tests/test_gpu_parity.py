@@ -287,3 +287,31 @@ def test_published_netlib_example_through_the_c_abi(cf, oracle, method, nsteps, 
         ys2, _, res2 = cf.cf_lowess_smooth(x, y, f, nsteps)
     assert np.array_equal(np.round(ys2, 3), want)
     assert np.array_equal(res2, y - ys2)
+
+
+@pytest.mark.parametrize("kind", ["exact_line", "one_outlier", "quantised", "tiny"])
+def test_robust_step_on_degenerate_residuals(cf, oracle, kind):
+    """The select behind the robustness step (:697-703) where all |res| share one bucket (exact
+    fit: res = 0 or a few ulp), where the two middle ranks differ, and on heavy ties."""
+    n, f, nsteps = 6001, 0.3, 2
+    x = cases.make_x("uniform", n, 7)
+    rng = np.random.default_rng(11)
+    if kind == "exact_line":
+        y = 2.0 * x + 1.0
+    elif kind == "one_outlier":
+        y = 2.0 * x + 1.0
+        y[n // 3] += 5.0
+    elif kind == "quantised":
+        y = np.round(cases.make_y(x, 7) * 4.0) / 4.0
+    else:
+        y = (2.0 * x + 1.0) + rng.choice([-1e-300, 0.0, 1e-300], n)
+    ref = oracle.lowess(x, y, f, nsteps)
+    ys, rw, res = cf.cf_lowess_smooth(x, y, f, nsteps)
+    assert cases.close(ys, ref["ys"], TOL)[0]
+    # the weights follow from (res, cmad) exactly: recompute the reference step on OUR residuals
+    fit = cf.lowess_smoothing()
+    fit.initialize(x, y, srt=False)
+    ys1, rw1, res1 = fit.run_from_rw(f, None, passes=2)
+    ys0, _, res0 = fit.run_from_rw(f, None, passes=1)
+    cmad, rw_ref = oracle.robust_weights(res0)
+    assert np.array_equal(rw1, rw_ref), kind

@@ -77,3 +77,60 @@ def test_median_and_sort_bit_exact(cf, oracle, n):
 
 def test_median_empty(cf):
     assert cf.median(np.zeros(0)) == 0.0
+
+
+def _adversarial(kind, n):
+    """Distributions that stress the radix select: everything in one round-0 bucket, the two
+    middle ranks in different buckets, ties at the median, signed zeros, infinities, denormals."""
+    rng = np.random.default_rng(len(kind) * 1000 + n)
+    if kind == "equal":
+        return np.full(n, 3.25)
+    if kind == "zeros":
+        x = np.zeros(n)
+        x[::2] = -0.0
+        return x
+    if kind == "two":
+        return rng.choice([-1.5, 2.5], size=n)
+    if kind == "split":                      # lower half negative, upper half positive: ranks straddle the sign
+        x = np.abs(rng.normal(size=n)) + 1.0
+        x[: n // 2] *= -1.0
+        return rng.permutation(x)
+    if kind == "narrow":                     # 1 + k ulp: only the lowest bits differ
+        return 1.0 + rng.integers(0, 1000, n) * np.finfo(np.float64).eps
+    if kind == "denormal":
+        return rng.integers(-50, 50, n).astype(np.float64) * 5e-324
+    if kind == "inf":
+        x = rng.normal(size=n)
+        x[rng.integers(0, n, max(n // 3, 1))] = np.inf
+        x[rng.integers(0, n, max(n // 3, 1))] = -np.inf
+        return x
+    if kind == "huge_range":
+        return rng.normal(size=n) * 10.0 ** rng.integers(-300, 300, n)
+    raise ValueError(kind)
+
+
+@pytest.mark.parametrize("kind", ["equal", "zeros", "two", "split", "narrow", "denormal", "inf", "huge_range"])
+@pytest.mark.parametrize("n", [2, 5, 64, 1000, 4097, 300_001])
+def test_median_adversarial_bit_exact(cf, kind, n):
+    x = _adversarial(kind, n)
+    s = np.sort(x)
+    want = s[n // 2] if n % 2 else 0.5 * (s[n // 2 - 1] + s[n // 2])     # median_dbl :280-292
+    got = cf.median(x.copy(), srt=False)
+    assert got == want or (np.isnan(got) and np.isnan(want)), (kind, n, got, want)
+
+
+def test_median_device_is_stream_ordered(cf):
+    """cf_median_device with stream = NULL runs on the legacy default stream (like
+    cf_moving_average_device), so it is ordered after work queued there."""
+    import ctypes as C
+
+    import torch
+    from curvefit_b200 import _lib
+    lib = _lib.load()
+    n = 2_000_001
+    x = torch.randn(n, dtype=torch.float64, device="cuda")
+    y = x * 2.0 + 1.0                          # queued on the default stream right before the call
+    out = torch.empty(1, dtype=torch.float64, device="cuda")
+    rc = lib.cf_median_device(C.c_void_p(y.data_ptr()), n, C.c_void_p(out.data_ptr()), None)
+    assert rc == 0
+    assert float(out.item()) == float(torch.median(y).item())
