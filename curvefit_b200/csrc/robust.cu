@@ -219,22 +219,52 @@ residual_hist0_kernel(const double* __restrict__ y, double* __restrict__ ys, dou
     hist0 += (size_t)blockIdx.y * bins;
     for (int k = threadIdx.x; k < bins; k += blockDim.x) sh[k] = 0u;
     __syncthreads();
+    // U independent elements per thread and trip: the loads of all U are in flight together
+    // (one CTA of 1024 threads per SM -- the 128 KB histogram -- would otherwise be latency bound)
+    constexpr int U = 4;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t i = (int64_t)begin + blockIdx.x * blockDim.x + threadIdx.x; i < end; i += stride) {
-        unsigned long long key;
+    for (int64_t i0 = (int64_t)begin + blockIdx.x * blockDim.x + threadIdx.x; i0 < end; i0 += U * stride) {
+        unsigned long long key[U];
+        bool ok[U];
         if (SRC == kSrcResidual) {
-            const int32_t l = max(leader[off + i], begin);
-            const double v = ys[off + l];
-            if (l != (int32_t)i) ys[off + i] = v;                               // :685-688
-            const double r = __dsub_rn(y[off + i], v);                          // :695
-            res[off + i] = r;
-            key = abs_key(r);                                                   // :697
-        } else if (SRC == kSrcAbs) {
-            key = abs_key(res[off + i]);
+            int32_t l[U];
+            double v[U], yy[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int64_t i = i0 + u * stride;
+                ok[u] = i < end;
+                l[u] = ok[u] ? max(leader[off + i], begin) : begin;
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int64_t i = i0 + u * stride;
+                v[u] = ok[u] ? ys[off + l[u]] : 0.0;
+                yy[u] = ok[u] ? y[off + i] : 0.0;
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int64_t i = i0 + u * stride;
+                if (ok[u]) {
+                    if (l[u] != (int32_t)i) ys[off + i] = v[u];                 // :685-688
+                    const double r = __dsub_rn(yy[u], v[u]);                    // :695
+                    res[off + i] = r;
+                    key[u] = abs_key(r);                                        // :697
+                }
+            }
         } else {
-            key = ordered_key(res[off + i]);
+            double v[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int64_t i = i0 + u * stride;
+                ok[u] = i < end;
+                v[u] = ok[u] ? res[off + i] : 0.0;
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) key[u] = SRC == kSrcAbs ? abs_key(v[u]) : ordered_key(v[u]);
         }
-        atomicAdd(&sh[(unsigned)(key >> shift0)], 1u);
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (ok[u]) atomicAdd(&sh[(unsigned)(key[u] >> shift0)], 1u);
     }
     __syncthreads();
     for (int k = threadIdx.x; k < bins; k += blockDim.x)

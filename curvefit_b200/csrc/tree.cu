@@ -519,10 +519,18 @@ struct Moments { double S0, S1, S2, T0, T1; };
 
 // One node inside a tricube range.  nsig = +1 left of xs (w = (1 + s^3)^3),
 // -1 right of xs (w = (1 - s^3)^3).
+template <bool SH>
+__device__ __forceinline__ double2 ldn(const double* p)
+{
+    if (SH) return *reinterpret_cast<const double2*>(p);      // staged node in shared memory
+    return ld2(p);
+}
+
+template <bool SH = false>
 __device__ __forceinline__ void take_tricube(const double* __restrict__ nd, double xs, double invh,
                                              double nsig, Moments& m)
 {
-    const double2 cd = ld2(nd);
+    const double2 cd = ldn<SH>(nd);
     const double beta = (cd.x - xs) * invh;       // s at the node centre
     const double alpha = cd.y * invh;             // ds/dv
     const double b2 = beta * beta, a2 = alpha * alpha;
@@ -554,12 +562,12 @@ __device__ __forceinline__ void take_tricube(const double* __restrict__ nd, doub
     double A[kKA], Bm[kKA];
 #pragma unroll
     for (int k = 0; k < kKA / 2; ++k) {
-        const double2 t = ld2(nd + 2 + 2 * k);
+        const double2 t = ldn<SH>(nd + 2 + 2 * k);
         A[2 * k] = t.x; A[2 * k + 1] = t.y;
     }
 #pragma unroll
     for (int k = 0; k < 6; ++k) {
-        const double2 t = ld2(nd + 2 + kKA + 2 * k);
+        const double2 t = ldn<SH>(nd + 2 + kKA + 2 * k);
         Bm[2 * k] = t.x; Bm[2 * k + 1] = t.y;     // Bm[11] is the node's zero pad
     }
     double D0 = 0.0, D1 = 0.0, D2 = 0.0, E0 = 0.0, E1 = 0.0;
@@ -580,19 +588,89 @@ __device__ __forceinline__ void take_tricube(const double* __restrict__ nd, doub
 }
 
 // One node inside the w = 1 core.
+template <bool SH = false>
 __device__ __forceinline__ void take_core(const double* __restrict__ nd, double xs, double invh,
                                           Moments& m)
 {
-    const double2 cd = ld2(nd);
+    const double2 cd = ldn<SH>(nd);
     const double beta = (cd.x - xs) * invh, alpha = cd.y * invh;
-    const double2 a01 = ld2(nd + 2);
-    const double2 a23 = ld2(nd + 4);
-    const double2 b01 = ld2(nd + 2 + kKA);
+    const double2 a01 = ldn<SH>(nd + 2);
+    const double2 a23 = ldn<SH>(nd + 4);
+    const double2 b01 = ldn<SH>(nd + 2 + kKA);
     m.S0 += a01.x;
     m.S1 += fma(beta, a01.x, alpha * a01.y);
     m.S2 += fma(beta * beta, a01.x, fma(2.0 * alpha * beta, a01.y, alpha * alpha * a23.x));
     m.T0 += b01.x;
     m.T1 += fma(beta, b01.x, alpha * b01.y);
+}
+
+// ---- warp-cooperative node staging ----------------------------------------------------------
+// The 32 lanes of a warp are 32 neighbouring output points: their node lists are almost the
+// same (the windows shift by about one element per point, a node covers >= 16), and the nodes
+// they need at the same step of the walk are NEIGHBOURS in the node array (SUF_g[a], SUF_g[a+1]
+// ...).  Instead of every lane fetching its own 256-byte node (13 LDG.128 per lane and node,
+// 32x redundant L1 traffic), the warp copies the kStage consecutive nodes starting at the
+// smallest index any lane asks for into shared memory with two 16-byte cp.async per lane
+// (1 KB, fully coalesced), and every lane whose node is among them evaluates it from there
+// (broadcast LDS).  Lanes whose node lies elsewhere wait for a later step; a lane consumes its
+// own list in its own order whatever the other lanes do, so a point's sums do not depend on
+// which warp it is in.  The copy for the NEXT step is in flight while this step's ~110 FP64
+// instructions per node run (double buffer; the next indices are known before the evaluation).
+constexpr int kStage = 4;            // nodes staged per warp and step
+constexpr int kStagePad = 34;        // doubles per staged node: 272 B, so that lanes on different
+                                     // slots read different banks
+constexpr int kStageLen = kStage * kStagePad;
+constexpr unsigned kNoNode = 0xffffffffu;
+
+__device__ __forceinline__ void cp_async16(double* smem, const double* gmem)
+{
+    const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// nodes [m, m + kStage) -> buf (the node array is padded by kStage nodes, so this never leaves it)
+__device__ __forceinline__ void stage_nodes(double* buf, const double* __restrict__ nodes, unsigned m)
+{
+    const int lane = threadIdx.x & 31;
+    const double* src = nodes + (size_t)m * kNodeLen;
+#pragma unroll
+    for (int h = 0; h < (kStage * kNodeLen) / 64; ++h) {
+        const int c = lane + 32 * h;                  // 16-byte chunk of the kStage * 256 bytes
+        const int q = c >> 4, o = (c & 15) * 2;
+        cp_async16(buf + q * kStagePad + o, src + q * kNodeLen + o);
+    }
+    cp_async_commit();
+}
+
+// The walk of one phase for a whole warp.  have/node: this lane's current item; advance():
+// moves the lane to its next item, returns false when its list is exhausted; tag(): per-item
+// value read BEFORE advance (the side of the tricube); take(staged node, tag).
+template <class Adv, class Tag, class Take>
+__device__ __forceinline__ void staged_walk(const double* __restrict__ nodes, double* stage, bool& have,
+                                            int32_t& node, Adv&& advance, Tag&& tag, Take&& take)
+{
+    constexpr unsigned kFull = 0xffffffffu;
+    unsigned m = __reduce_min_sync(kFull, have ? (unsigned)node : kNoNode);
+    if (m == kNoNode) return;
+    int buf = 0;
+    stage_nodes(stage, nodes, m);
+    for (;;) {
+        const unsigned cur = have ? (unsigned)node : kNoNode;
+        const bool served = cur - m < (unsigned)kStage;        // cur >= m for every lane that has an item
+        const double tg = tag();
+        if (served) have = advance();
+        const unsigned m2 = __reduce_min_sync(kFull, have ? (unsigned)node : kNoNode);
+        cp_async_wait_all();
+        __syncwarp();                                          // this step's nodes have landed for all lanes
+        if (m2 != kNoNode) stage_nodes(stage + (buf ^ 1) * kStageLen, nodes, m2);
+        if (served) take(stage + buf * kStageLen + (cur - m) * kStagePad, tg);
+        if (m2 == kNoNode) break;
+        buf ^= 1;
+        m = m2;
+    }
+    __syncwarp();
 }
 
 // One thread per output point.  Three phases, each a warp-convergent loop in
@@ -625,6 +703,9 @@ tree_eval_kernel(const TreeParams prm)
         return v;
     };
     const double* __restrict__ nodes = prm.nodes + (size_t)blockIdx.y * prm.total * kNodeLen;
+    // PF == 2: per-warp double buffer of staged nodes (see staged_walk)
+    __shared__ __align__(16) double stage_all[PF == 2 ? (NT / 32) * 2 * kStageLen : 2];
+    double* stage = stage_all + (PF == 2 ? (threadIdx.x >> 5) * 2 * kStageLen : 0);
 
     // tie followers copy their leader's value later (robust.cu); a shard that starts
     // inside a tie group fits its first point in the leader's place (as fit.cu)
@@ -685,7 +766,10 @@ tree_eval_kernel(const TreeParams prm)
             return false;
         };
         bool have = advance();
-        if (PF == 0) {
+        if (PF == 2) {
+            staged_walk(nodes, stage, have, node, advance, [&]() { return nsig; },
+                        [&](const double* nd, double sg) { take_tricube<true>(nd, xs, invh, sg, m); });
+        } else if (PF == 0) {
             while (__any_sync(kFull, have)) {
                 if (have) {
                     take_tricube(nodes + (size_t)node * kNodeLen, xs, invh, nsig, m);
@@ -723,10 +807,15 @@ tree_eval_kernel(const TreeParams prm)
         }
         int32_t node = 0;
         bool have = w.next(prm, node);
-        while (__any_sync(kFull, have)) {
-            if (have) {
-                take_core(nodes + (size_t)node * kNodeLen, xs, invh, m);
-                have = w.next(prm, node);
+        if (PF == 2) {
+            staged_walk(nodes, stage, have, node, [&]() { return w.next(prm, node); }, []() { return 0.0; },
+                        [&](const double* nd, double) { take_core<true>(nd, xs, invh, m); });
+        } else {
+            while (__any_sync(kFull, have)) {
+                if (have) {
+                    take_core(nodes + (size_t)node * kNodeLen, xs, invh, m);
+                    have = w.next(prm, node);
+                }
             }
         }
     }
@@ -868,7 +957,8 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
         }
     }
     prm.total = total;
-    const size_t need = sizeof(double) * kNodeLen * (size_t)total * (size_t)h->nseries;
+    // + kStage nodes: the evaluator stages kStage consecutive nodes from any index it needs
+    const size_t need = sizeof(double) * kNodeLen * ((size_t)total * (size_t)h->nseries + kStage);
     if (need > h->tree_bytes) {
         cudaFree(h->tree);
         h->tree = nullptr;
@@ -940,13 +1030,18 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
     // 7 CTAs of 128 threads per SM (72 registers) + L1 prefetch of the next node; the
     // others are kept for measurement (B200, n = 1e8 smooth: 5 CTAs 143.2 ms, 6: 128.6,
     // 7: 125.7, 7 + prefetch 125.3)
-    static const int variant = dev_env("CF_TREE_EVAL") ? atoi(dev_env("CF_TREE_EVAL")) : 7;
+    static const int variant = dev_env("CF_TREE_EVAL") ? atoi(dev_env("CF_TREE_EVAL")) : 72;
     const dim3 eg((cntp + 127) / 128, h->nseries);
     switch (variant) {
+#ifdef CF_DEVELOPMENT
     case 5:  tree_eval_kernel<128, 5, 0><<<eg, 128, 0, h->stream>>>(prm); break;
     case 6:  tree_eval_kernel<128, 6, 0><<<eg, 128, 0, h->stream>>>(prm); break;
     case 70: tree_eval_kernel<128, 7, 0><<<eg, 128, 0, h->stream>>>(prm); break;
-    default: tree_eval_kernel<128, 7, 1><<<eg, 128, 0, h->stream>>>(prm); break;
+    case 71: tree_eval_kernel<128, 7, 1><<<eg, 128, 0, h->stream>>>(prm); break;   // round 1: per-lane node loads
+    case 62: tree_eval_kernel<128, 6, 2><<<eg, 128, 0, h->stream>>>(prm); break;
+    case 52: tree_eval_kernel<128, 5, 2><<<eg, 128, 0, h->stream>>>(prm); break;
+#endif
+    default: tree_eval_kernel<128, 7, 2><<<eg, 128, 0, h->stream>>>(prm); break;   // warp-staged nodes
     }
     CF_CUDA(cudaGetLastError());
     h->launches++;

@@ -115,8 +115,10 @@ def test_median_adversarial_bit_exact(cf, kind, n):
     x = _adversarial(kind, n)
     s = np.sort(x)
     want = s[n // 2] if n % 2 else 0.5 * (s[n // 2 - 1] + s[n // 2])     # median_dbl :280-292
-    got = cf.median(x.copy(), srt=False)
+    a = x.copy()
+    got = cf.median(a)                  # srt = .true.: select on the device, then x is left sorted
     assert got == want or (np.isnan(got) and np.isnan(want)), (kind, n, got, want)
+    assert np.array_equal(a, s)
 
 
 def test_median_device_is_stream_ordered(cf):
