@@ -28,7 +28,7 @@ $(OBJDIR)/%.o: curvefit_b200/csrc/%.cu curvefit_b200/csrc/common.cuh curvefit_b2
 
 $(LIB): $(OBJ)
 	@mkdir -p $(dir $(LIB))
-	$(NVCC) $(ARCH) -shared -o $@ $(OBJ) -lcudart -ccbin /usr/bin/g++
+	$(NVCC) $(ARCH) -shared -o $@ $(OBJ) -lcudart -Xcompiler -pthread -ccbin /usr/bin/g++
 
 oracle:
 	$(MAKE) -C oracle

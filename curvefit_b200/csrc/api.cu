@@ -4,6 +4,7 @@
 // Fortran shim binds.  No CPU fallback: every entry point that does work needs
 // a CUDA device and reports CF_DEVICE_ERROR otherwise.
 #include <math.h>
+#include <math_constants.h>
 #include <stdarg.h>
 #include <stdlib.h>
 #include <string.h>
@@ -26,6 +27,8 @@ void set_error(const char* fmt, ...)
     vsnprintf(g_err, sizeof(g_err), fmt, ap);
     va_end(ap);
 }
+
+const char* last_error_text() { return g_err; }
 
 int cuda_fail(cudaError_t e, const char* what, const char* file, int line)
 {
@@ -302,6 +305,73 @@ int32_t cf_lowess_init(cf_lowess* h, const double* x, const double* y, int32_t n
 {
     return init_common(h, x, y, n, sort, cudaMemcpyHostToDevice);
 }
+
+}  // extern "C"
+
+namespace cf {
+
+// ls_init's allocation part (:758-789) for a series of n points, nothing uploaded yet
+// (multi.cu: a rank of cf_lowess_smooth_multi receives only the elements its windows reach).
+int layout_series(cf_lowess* h, int32_t n)
+{
+    if (!h || n < 1) { set_error("Input array sizes must match."); return CF_ARRAY_SIZE_ERROR; }
+    CF_TRY(use_device(h));
+    h->init = false;
+    h->win_f = -1.0;
+    h->delta_built = -1.0;
+    h->nseries = 1;
+    CF_TRY(reserve(h, n));
+    h->n = n;
+    compute_shard(h);
+    CF_TRY(reserve_rw(h));
+    h->init = true;
+    return CF_OK;
+}
+
+// x outside [lo, hi] <- -inf below, +inf above: the series stays ascending, so every search of
+// windows.cu that probes beyond the uploaded elements still meets a monotone predicate and ends
+// on the same index as on the whole series (the answers lie inside [lo, hi] by construction).
+// x(1) and x(n) keep their values: lowest() needs range = x(n) - x(1) (:535), and a probe that
+// lands on them sees what it would see on the whole series.
+__global__ void __launch_bounds__(256)
+sentinel_kernel(double* __restrict__ x, int32_t n, int32_t lo, int32_t hi)
+{
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int64_t below = lo > 1 ? lo - 1 : 0;                         // indices 1 .. lo - 1
+    const int64_t above = (int64_t)n - 2 - hi > 0 ? (int64_t)n - 2 - hi : 0;   // hi + 1 .. n - 2
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < below + above; k += stride) {
+        if (k < below) x[1 + k] = -CUDART_INF;
+        else x[(int64_t)hi + 1 + (k - below)] = CUDART_INF;
+    }
+}
+
+// Elements [lo, hi] of the host series -> the same positions of the handle's x, y (asynchronous
+// on the handle's stream); the rest of x becomes sentinels (first and last element excepted),
+// the rest of y is left as it is (nothing reads it: fits, tree nodes and residuals touch
+// [min lo9, max hi9] and the shard only).
+int upload_span(cf_lowess* h, const double* x, const double* y, int32_t lo, int32_t hi)
+{
+    if (!h || !h->init || lo < 0 || hi >= h->n || lo > hi) { set_error("bad span [%d, %d]", (int)lo, (int)hi); return CF_INVALID_INPUT_ERROR; }
+    CF_TRY(use_device(h));
+    h->win_f = -1.0;                                   // new data: new neighbourhoods
+    h->delta_built = -1.0;
+    const size_t bytes = sizeof(double) * (size_t)(hi - lo + 1);
+    CF_CUDA(cudaMemcpyAsync(h->x + lo, x + lo, bytes, cudaMemcpyHostToDevice, h->stream));
+    CF_CUDA(cudaMemcpyAsync(h->y + lo, y + lo, bytes, cudaMemcpyHostToDevice, h->stream));
+    if (lo > 0) CF_CUDA(cudaMemcpyAsync(h->x, x, sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    if (hi < h->n - 1)
+        CF_CUDA(cudaMemcpyAsync(h->x + (h->n - 1), x + (h->n - 1), sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    if (lo > 1 || hi < h->n - 2) {
+        sentinel_kernel<<<296, 256, 0, h->stream>>>(h->x, h->n, lo, hi);
+        CF_CUDA(cudaGetLastError());
+        h->launches++;
+    }
+    return CF_OK;
+}
+
+}  // namespace cf
+
+extern "C" {
 
 int32_t cf_lowess_init_device(cf_lowess* h, const void* d_x, const void* d_y, int32_t n, int32_t sort)
 {

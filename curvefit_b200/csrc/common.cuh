@@ -269,4 +269,10 @@ int sort_xy_inplace(double* x_io, double* y_io, int32_t n, double* x_out, double
 
 int fp64_peak(int device, double ms_target, double* tflops, double* mhz);
 
+// api.cu, used by multi.cu (cf_lowess_smooth_multi): allocate for n points without uploading;
+// upload elements [lo, hi] only (x outside becomes -inf / +inf sentinels)
+int layout_series(cf_lowess* h, int32_t n);
+int upload_span(cf_lowess* h, const double* x, const double* y, int32_t lo, int32_t hi);
+const char* last_error_text();
+
 }  // namespace cf

@@ -1,0 +1,208 @@
+// multi.cu -- cf_lowess_smooth_multi: lowess() (src/curvefit_regression.f90:625-715, as
+// ls_smooth calls it, :866) of ONE series over several GPUs of one box from ONE process --
+// what a Fortran program calling fit%smooth(f) can reach through the bind(C) shim.
+//
+// The sorted index range is cut into `ndev` equal blocks of output points (same
+// partition and the same kernels as the one-process-per-GPU path of distributed.py).  One
+// host thread per device:
+//   * uploads only the elements its block's windows can reach -- [begin - ns, end - 1 + ns]
+//     widened over ties: the (ns-1)-point halo -- not the whole series;
+//   * runs the passes (cf_lowess_run on a peer-attached handle: the histogram all-reduce of the
+//     median, the candidate exchange and the halo weights cross NVLink inside the kernels,
+//     peer.cu; the peers are mapped with cudaDeviceEnablePeerAccess, no IPC);
+//   * copies its own block of ys, rw, res straight into the caller's arrays.
+// The handles, their buffers and the peer mapping are kept between calls of the same n and
+// device list (a caller looping over smooth() pays for them once); cf_lowess_multi_release()
+// frees them.
+#include <algorithm>
+#include <condition_variable>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "common.cuh"
+
+namespace cf {
+namespace {
+
+struct MultiCtx {
+    std::vector<int> devs;
+    int32_t n = 0;
+    std::vector<cf_lowess*> hs;
+};
+
+std::mutex g_multi_mu;            // one multi-GPU smooth at a time per process
+MultiCtx* g_multi = nullptr;
+
+void multi_free(MultiCtx* c)
+{
+    if (!c) return;
+    for (cf_lowess* h : c->hs) if (h) { cudaSetDevice(h->device); cudaStreamSynchronize(h->stream); }
+    for (cf_lowess* h : c->hs) if (h) { cudaSetDevice(h->device); peer_detach(h); }
+    for (cf_lowess* h : c->hs) cf_lowess_destroy(h);
+    delete c;
+}
+
+int multi_build(const std::vector<int>& devs, int32_t n, MultiCtx** out)
+{
+    MultiCtx* c = new MultiCtx();
+    c->devs = devs;
+    c->n = n;
+    c->hs.assign(devs.size(), nullptr);
+    int rc = CF_OK;
+    for (size_t r = 0; r < devs.size() && rc == CF_OK; ++r) {
+        rc = cf_lowess_create(&c->hs[r], devs[r], nullptr);
+        if (rc == CF_OK) rc = cf_lowess_set_shard(c->hs[r], (int32_t)r, (int32_t)devs.size());
+        if (rc == CF_OK) rc = layout_series(c->hs[r], n);
+    }
+    if (rc == CF_OK) rc = cf_lowess_peer_attach_local(c->hs.data(), (int32_t)devs.size());
+    if (rc != CF_OK) { multi_free(c); return rc; }
+    *out = c;
+    return CF_OK;
+}
+
+// all threads of one call meet here between the upload and the collective run
+struct HostBarrier {
+    std::mutex mu;
+    std::condition_variable cv;
+    int waiting = 0, total = 0, gen = 0;
+    void arrive()
+    {
+        std::unique_lock<std::mutex> lk(mu);
+        const int g = gen;
+        if (++waiting == total) { waiting = 0; ++gen; cv.notify_all(); }
+        else cv.wait(lk, [&] { return gen != g; });
+    }
+};
+
+}  // namespace
+}  // namespace cf
+
+using namespace cf;
+
+extern "C" {
+
+int32_t cf_lowess_multi_release(void)
+{
+    std::lock_guard<std::mutex> lk(g_multi_mu);
+    int dev = 0;
+    const bool have = cudaGetDevice(&dev) == cudaSuccess;
+    multi_free(g_multi);
+    g_multi = nullptr;
+    if (have) cudaSetDevice(dev);
+    return CF_OK;
+}
+
+int32_t cf_lowess_smooth_multi(const double* x_sorted, const double* y, int32_t n, double f,
+                               int32_t nsteps, const int32_t* devices, int32_t ndev,
+                               double* ys, double* rw, double* res)
+{
+    if (n < 0 || (n > 0 && (!x_sorted || !y || !ys))) {
+        set_error("Input array sizes must match.");
+        return CF_ARRAY_SIZE_ERROR;
+    }
+    if (nsteps < 0) { set_error("nsteps must be >= 0"); return CF_INVALID_INPUT_ERROR; }
+    int visible = 0;
+    {
+        const cudaError_t e = cudaGetDeviceCount(&visible);
+        if (e != cudaSuccess || visible == 0) {
+            set_error("no CUDA device available (%s); libcurvefit_cuda has no CPU fallback",
+                      e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+            return CF_DEVICE_ERROR;
+        }
+    }
+    std::vector<int> devs;
+    if (!devices || ndev <= 0) {
+        for (int d = 0; d < visible && d < kMaxPeers; ++d) devs.push_back(d);
+    } else {
+        if (ndev > kMaxPeers) { set_error("at most %d devices", kMaxPeers); return CF_INVALID_INPUT_ERROR; }
+        for (int k = 0; k < ndev; ++k) {
+            if (devices[k] < 0 || devices[k] >= visible || std::count(devs.begin(), devs.end(), (int)devices[k])) {
+                set_error("bad device list (entry %d = %d; %d visible, no duplicates)", k, (int)devices[k], visible);
+                return CF_INVALID_INPUT_ERROR;
+            }
+            devs.push_back(devices[k]);
+        }
+    }
+    int caller_dev = 0;
+    CF_CUDA(cudaGetDevice(&caller_dev));
+    // short series: the blocks would be a few tiles each -- one GPU does it
+    if (devs.size() == 1 || (int64_t)n < (int64_t)4096 * (int64_t)devs.size()) {
+        CF_CUDA(cudaSetDevice(devs[0]));
+        const int rc = cf_lowess_smooth(x_sorted, y, n, f, nsteps, ys, rw, res);
+        cudaSetDevice(caller_dev);
+        return rc;
+    }
+    if (!(f == f)) { set_error("f is NaN"); return CF_INVALID_INPUT_ERROR; }
+
+    std::lock_guard<std::mutex> lk(g_multi_mu);
+    if (g_multi && (g_multi->n != n || g_multi->devs != devs)) { multi_free(g_multi); g_multi = nullptr; }
+    if (!g_multi) {
+        const int rc = multi_build(devs, n, &g_multi);
+        if (rc != CF_OK) { cudaSetDevice(caller_dev); return rc; }
+    }
+    MultiCtx* c = g_multi;
+    const int N = (int)devs.size();
+    const int32_t ns = cf_lowess_span(n, f);
+    const int method = cf_default_method();
+    std::vector<int> rcs((size_t)N, CF_OK);
+    std::vector<std::string> msgs((size_t)N);
+    HostBarrier bar;
+    bar.total = N;
+    bool abort_run = false;       // written by rank threads before the barrier, read after it
+
+    auto work = [&](int r) {
+        cf_lowess* h = c->hs[(size_t)r];
+        auto fail = [&](int rc) { rcs[(size_t)r] = rc; msgs[(size_t)r] = last_error_text(); };
+        int rc = CF_OK;
+        if (cudaSetDevice(h->device) != cudaSuccess) rc = CF_DEVICE_ERROR;
+        h->method = method;
+        // the elements the windows of [begin, end) can reach (windows.cu reads x(L + ns) for
+        // L <= i): [begin - ns, end - 1 + ns], widened over ties -- a window with h = 0 takes
+        // every point equal to xs (:546), and the leader of a tie group may lie below
+        int64_t lo = (int64_t)h->begin - ns, hi = (int64_t)h->end - 1 + ns;
+        if (lo < 0) lo = 0;
+        if (hi > n - 1) hi = n - 1;
+        lo = std::lower_bound(x_sorted, x_sorted + lo, x_sorted[lo]) - x_sorted;
+        hi = (std::upper_bound(x_sorted + hi, x_sorted + n, x_sorted[hi]) - x_sorted) - 1;
+        if (rc == CF_OK) rc = upload_span(h, x_sorted, y, (int32_t)lo, (int32_t)hi);
+        if (rc != CF_OK) {
+            fail(rc);
+            std::lock_guard<std::mutex> g(bar.mu);
+            abort_run = true;
+        }
+        bar.arrive();             // nobody enters the collective run unless every rank can
+        if (abort_run) return;
+        rc = cf_lowess_run(h, f, nsteps, nullptr);
+        if (rc == CF_OK) {
+            const size_t cnt = (size_t)(h->end - h->begin), b = sizeof(double) * cnt;
+            cudaError_t e = cudaMemcpyAsync(ys + h->begin, h->ys + h->begin, b, cudaMemcpyDeviceToHost, h->stream);
+            if (e == cudaSuccess && rw && nsteps > 0)
+                e = cudaMemcpyAsync(rw + h->begin, h->rw + h->begin, b, cudaMemcpyDeviceToHost, h->stream);
+            if (e == cudaSuccess && res)
+                e = cudaMemcpyAsync(res + h->begin, h->res + h->begin, b, cudaMemcpyDeviceToHost, h->stream);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+            if (e != cudaSuccess) rc = cuda_fail(e, "cf_lowess_smooth_multi download", __FILE__, __LINE__);
+        }
+        if (rc != CF_OK) fail(rc);
+    };
+    std::vector<std::thread> th;
+    for (int r = 1; r < N; ++r) th.emplace_back(work, r);
+    work(0);
+    for (auto& t : th) t.join();
+    cudaSetDevice(caller_dev);
+    for (int r = 0; r < N; ++r) {
+        if (rcs[(size_t)r] != CF_OK) {
+            set_error("device %d (block %d of %d): %s", devs[(size_t)r], r, N, msgs[(size_t)r].c_str());
+            // a failed collective leaves epochs and flags in an unknown state: start afresh next time
+            multi_free(g_multi);
+            g_multi = nullptr;
+            cudaSetDevice(caller_dev);
+            return rcs[(size_t)r];
+        }
+    }
+    return CF_OK;
+}
+
+}  // extern "C"

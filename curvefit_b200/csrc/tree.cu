@@ -827,13 +827,15 @@ tree_eval_kernel(const TreeParams prm)
         // stream is j1 + k in its first piece, j2 + (k - c1) in its second.  Inside A an element
         // belongs to the w = 1 core iff j >= l1, inside B iff j <= r1 (:547-551).
         const bool valid = i >= 0;
-        const size_t so = soff();
-        const double* __restrict__ x = prm.x + so;
-        const double* __restrict__ y = prm.y + so;
-        const double* __restrict__ rw = prm.rw ? prm.rw + so : nullptr;
+        // the three arrays as per-thread pointers the compiler cannot fold back into
+        // (index + series offset) arithmetic: one IMAD.WIDE per load instead of seven instructions
+        const double* x = prm.x + soff();
+        const double* y = prm.y + soff();
+        const double* rw = prm.rw ? prm.rw + soff() : nullptr;
+        asm volatile("" : "+l"(x), "+l"(y), "+l"(rw));
         int32_t l9 = 0, r9 = -1, l1 = 0, r1 = -1;
         if (valid) {
-            const size_t pi = so + i;
+            const size_t pi = soff() + i;
             l9 = ldv(prm.w.lo9 + pi); r9 = ldv(prm.w.hi9 + pi);
             l1 = ldv(prm.w.lo1 + pi); r1 = ldv(prm.w.hi1 + pi);
         }
@@ -844,19 +846,22 @@ tree_eval_kernel(const TreeParams prm)
         const int32_t c1a = valid ? max(hdL - l9, 0) : 0, ca = c1a + (valid ? max(hdC - tlL, 0) : 0);
         const int32_t c1b = valid ? max(hdR - tlC, 0) : 0, cb = c1b + (valid ? max(r9 + 1 - tlR, 0) : 0);
         const int32_t d2a = tlL - c1a, d2b = tlR - c1b;           // j = d2 + k in the second piece
+        // last element of each stream (any readable index when the stream is empty): lanes that
+        // have run out keep reading it with weight zero
         const int32_t safe = valid ? i : 0;
+        const int32_t enda1 = ca > c1a ? d2a + ca - 1 : (ca > 0 ? l9 + ca - 1 : safe);
+        const int32_t endb1 = cb > c1b ? d2b + cb - 1 : (cb > 0 ? tlC + cb - 1 : safe);
         Moments mb = {0.0, 0.0, 0.0, 0.0, 0.0};
         const int32_t kmax = max(ca, cb);
         for (int32_t k = 0; __any_sync(kFull, k < kmax); ++k) {
-            const bool ona = k < ca, onb = k < cb;
-            const int32_t ja = ona ? (k < c1a ? l9 + k : d2a + k) : safe;
-            const int32_t jb = onb ? (k < c1b ? tlC + k : d2b + k) : safe;
+            const int32_t ja = min((k < c1a ? l9 : d2a) + k, enda1);
+            const int32_t jb = min((k < c1b ? tlC : d2b) + k, endb1);
             {
                 const double q = (x[ja] - xs) * invh;
                 const double tt = fma(-(q * q), fabs(q), 1.0);
                 double wgt = (tt * tt) * tt;
                 wgt = ja >= l1 ? 1.0 : wgt;
-                wgt = ona ? wgt : 0.0;
+                wgt = k < ca ? wgt : 0.0;
                 const double wr = rw ? wgt * rw[ja] : wgt;
                 const double wq = wr * q;
                 const double yj = y[ja];
@@ -871,7 +876,7 @@ tree_eval_kernel(const TreeParams prm)
                 const double tt = fma(-(q * q), fabs(q), 1.0);
                 double wgt = (tt * tt) * tt;
                 wgt = jb <= r1 ? 1.0 : wgt;
-                wgt = onb ? wgt : 0.0;
+                wgt = k < cb ? wgt : 0.0;
                 const double wr = rw ? wgt * rw[jb] : wgt;
                 const double wq = wr * q;
                 const double yj = y[jb];
@@ -983,7 +988,9 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
     int level = 1;
     int g0 = 1;
     if (fused) {
-        const bool chain = prm.ngroups >= 1;
+        // the level-1 chain is built inside the block launch when its blocks are small enough to be
+        // the launch's blocks; wider chain blocks get their own launch after the binary levels
+        const bool chain = prm.ngroups >= 1 && prm.cbits[1] <= 9;
         int cb = chain ? prm.cbits[1] : 8;
         if (cb > L - 1) cb = L - 1;
         // few blocks: 128 threads per block (shortest critical path); many: one warp per block

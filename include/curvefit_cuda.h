@@ -92,6 +92,23 @@ CF_API int32_t cf_lowess_smooth_batched(const double* x_sorted, const double* y,
                                         int32_t nsteps,
                                         double* ys, double* rw, double* res);
 
+/* lowess() of ONE series over several GPUs of one box, from one process (multi.cu) -- the
+ * multi-GPU form of cf_lowess_smooth and what the Fortran shim's smooth() binds
+ * (src/curvefit_regression.f90:832-868, ls_smooth).  The sorted index range is cut into ndev
+ * equal blocks of output points; device k uploads only the elements its block's windows
+ * reach (block + the (ns-1)-point halo on either side), the robustness step's exchanges cross
+ * NVLink inside the kernels (peer.cu; the devices must be peer-accessible), and every device
+ * writes its own block of ys, rw, res into the caller's arrays.  Results are bit-identical to
+ * cf_lowess_smooth.  devices = NULL or ndev <= 0: all visible devices (at most 8).  One device,
+ * or fewer than 4096 points per device: cf_lowess_smooth on devices[0].  The handles and the
+ * peer mapping are kept between calls with the same n and device list;
+ * cf_lowess_multi_release() frees them.  Calls are serialised per process. */
+CF_API int32_t cf_lowess_smooth_multi(const double* x_sorted, const double* y, int32_t n,
+                                      double f, int32_t nsteps,
+                                      const int32_t* devices, int32_t ndev,
+                                      double* ys, double* rw, double* res);
+CF_API int32_t cf_lowess_multi_release(void);
+
 /* ------------------------------------------------------------------------
  * Neighbours of the LOWESS path (stats.cu).
  * ---------------------------------------------------------------------- */
