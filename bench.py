@@ -347,6 +347,7 @@ def measure_series(env, name, method, steps, warmup, want_e2e, clocks=None, samp
            "gpu_launches": launches, "fit_launches": fit_launches, "ns": ns}
     out["_fit_ms"] = stage["fit"]
 
+    ys_solo = None
     # ---- the sharded result against a single-GPU run of the same series (outside the timed region)
     if world > 1 and compare_single:
         job.gather_results(with_rw=True)
@@ -368,7 +369,8 @@ def measure_series(env, name, method, steps, warmup, want_e2e, clocks=None, samp
                                     "speedup_vs_single_gpu_same_box": float(st1.ms_total) / out["ms_per_step"]}
             assert d <= 1e-12 * max(out["vs_single_gpu"]["max_abs_ys"], 1.0), f"sharded ys differs by {d}"
             solo.close()
-            del ys1, ysN
+            ys_solo = ys1
+            del ysN
         env.barrier()
 
     # ---- e2e: HOST buffers in, HOST buffers out, copies inside the timed region ---------------
@@ -392,21 +394,65 @@ def measure_series(env, name, method, steps, warmup, want_e2e, clocks=None, samp
                       "api": "cf_lowess_smooth(host x, y -> host ys, rw, res), pinned buffers, wall clock"}
         del xp, yp, outs
     elif want_e2e:
+        from curvefit_b200.distributed import SharedHostArray
         xp, yp = env.pinned(x), env.pinned(y)
-        outs = tuple(env.pinned_empty(n) for _ in range(3)) if rank == 0 else None
-        job.smooth_host(xp, yp, f, nsteps, outs)
+        shared = [SharedHostArray(n) for _ in range(3)]      # ys, rw, res: one host result all ranks map
+        outs = tuple(a.array for a in shared)
+        job.smooth_host(xp, yp, f, nsteps, outs, shared_out=True)
         reps = max(1, min(steps, 3))
         env.barrier()
         t0 = time.perf_counter()
         for _ in range(reps):
-            job.smooth_host(xp, yp, f, nsteps, outs)
+            job.smooth_host(xp, yp, f, nsteps, outs, shared_out=True)
         env.barrier()
         dt = env.max_over_ranks([(time.perf_counter() - t0) / reps])[0]
-        out["e2e"] = {"value": n / dt, "unit": "points/s", "h2d_bytes_per_step": 16 * n * world,
+        up = torch.tensor([float(job.last_upload)], device="cuda", dtype=torch.float64)
+        env.dist.all_reduce(up)
+        out["e2e"] = {"value": n / dt, "unit": "points/s", "h2d_bytes_per_step": int(16 * up.item()),
                       "d2h_bytes_per_step": 24 * n, "ms_per_step": dt * 1e3,
-                      "api": "ShardedLowess.smooth_host(host x, y on every rank -> host ys, rw, res on "
-                             "rank 0), pinned buffers, wall clock, max over ranks"}
-        del xp, yp, outs
+                      "api": "ShardedLowess.smooth_host(host x, y -> host ys, rw, res in shared page-locked memory): "
+                             "each rank uploads its block + (ns-1)-point halo and writes its own block of the "
+                             "result; wall clock incl. the closing barrier, max over ranks"}
+        if rank == 0 and ys_solo is not None:                   # the assembled host result vs one GPU
+            d = float(np.max(np.abs(outs[0] - ys_solo)))
+            out["e2e"]["max_abs_diff_ys_vs_single_gpu"] = d
+            assert d <= 1e-12 * max(float(np.max(np.abs(ys_solo))), 1.0), f"e2e ys differs by {d}"
+        env.barrier()
+        for a in shared:
+            a.close()
+        del xp, yp, outs, shared
+        # the same series through the C ABI from ONE process: cf_lowess_smooth_multi on rank 0
+        # drives all `world` devices (one host thread each) while the other ranks wait
+        if rank == 0:
+            xp, yp = env.pinned(x), env.pinned(y)
+            outs = tuple(env.pinned_empty(n) for _ in range(3))
+            devs = (C.c_int32 * world)(*range(world))
+            regression.set_default_method(method)
+            try:
+                call = lambda: lib.cf_lowess_smooth_multi(regression._dp(xp), regression._dp(yp), n, float(f),
+                                                          int(nsteps), devs, world, *(regression._dp(o) for o in outs))
+                rc = call()                                                   # builds and attaches the handles
+                if rc == 0:
+                    reps = max(1, min(steps, 3))
+                    t0 = time.perf_counter()
+                    for _ in range(reps):
+                        rc = rc or call()
+                    dt1 = (time.perf_counter() - t0) / reps
+                if rc == 0 and ys_solo is not None:
+                    d = float(np.max(np.abs(outs[0] - ys_solo)))
+                    assert d <= 1e-12 * max(float(np.max(np.abs(ys_solo))), 1.0), f"cf_lowess_smooth_multi ys differs by {d}"
+                if rc == 0:
+                    out["e2e_c_abi_one_process"] = {
+                        "value": n / dt1, "unit": "points/s", "ms_per_step": dt1 * 1e3, "devices": world,
+                        "api": "cf_lowess_smooth_multi(host x, y -> host ys, rw, res) from rank 0's process alone, "
+                               "one host thread per device, pinned buffers, wall clock"}
+                else:
+                    out["e2e_c_abi_one_process"] = {"error": _lib.last_error()}
+            finally:
+                regression.set_default_method("direct")
+                lib.cf_lowess_multi_release()
+            del xp, yp, outs
+        env.barrier()
     else:
         out["e2e"] = None
 

@@ -9,6 +9,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <atomic>
 #include <mutex>
 #include <new>
@@ -256,6 +257,8 @@ void cf_lowess_destroy(cf_lowess* h)
     cudaFree(h->tree);
     delta_free(h);
     for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
+    for (auto& ev : h->ev_copy) if (ev) cudaEventDestroy(ev);
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -369,9 +372,66 @@ int upload_span(cf_lowess* h, const double* x, const double* y, int32_t lo, int3
     return CF_OK;
 }
 
+// The elements the windows of output points [begin, end) can reach, computed on the host from
+// the sorted abscissas: windows.cu reads x(L + ns) for L <= i, so [begin - ns, end - 1 + ns],
+// widened over ties -- a window with h = 0 takes every point equal to xs (:546), and the leader
+// of a tie group may lie below.  A superset of [min lo9, max hi9].
+void shard_span_host(const double* x, int32_t n, int32_t ns, int32_t begin, int32_t end, int32_t* lo_out,
+                     int32_t* hi_out)
+{
+    int64_t lo = (int64_t)begin - ns, hi = (int64_t)end - 1 + ns;
+    if (lo < 0) lo = 0;
+    if (hi > n - 1) hi = n - 1;
+    if (hi < lo) hi = lo;
+    lo = std::lower_bound(x, x + lo, x[lo]) - x;
+    hi = (std::upper_bound(x + hi, x + n, x[hi]) - x) - 1;
+    *lo_out = (int32_t)lo;
+    *hi_out = (int32_t)hi;
+}
+
 }  // namespace cf
 
 extern "C" {
+
+int32_t cf_lowess_shard_span(const cf_lowess* h, const double* x_sorted, int32_t n, double f,
+                             int32_t* first, int32_t* last)
+{
+    if (!h || !x_sorted || n < 1 || !first || !last) { set_error("null argument"); return CF_INVALID_INPUT_ERROR; }
+    int64_t per = ((int64_t)n + h->nranks - 1) / h->nranks;
+    per = (per + kTile - 1) / kTile * kTile;
+    if (per < kTile) per = kTile;
+    const int64_t b = (int64_t)h->rank * per;
+    const int32_t begin = (int32_t)(b < n ? b : n), end = (int32_t)(b + per < n ? b + per : n);
+    int32_t lo = 0, hi = 0;
+    shard_span_host(x_sorted, n, cf_lowess_span(n, f), begin < n ? begin : n - 1, end, &lo, &hi);
+    *first = lo + 1;
+    *last = hi + 1;
+    return CF_OK;
+}
+
+int32_t cf_lowess_init_span(cf_lowess* h, const double* x_sorted, const double* y, int32_t n,
+                            int32_t first, int32_t last)
+{
+    if (!h) { set_error("null handle"); return CF_INVALID_INPUT_ERROR; }
+    if (n < 1 || !x_sorted || !y) { set_error("Input array sizes must match."); return CF_ARRAY_SIZE_ERROR; }
+    if (first < 1 || last > n || first > last) { set_error("bad span [%d, %d] of %d", (int)first, (int)last, (int)n); return CF_INVALID_INPUT_ERROR; }
+    CF_TRY(layout_series(h, n));
+    return upload_span(h, x_sorted, y, first - 1, last - 1);
+}
+
+int32_t cf_lowess_fetch_block(cf_lowess* h, double* ys, double* rw, double* res)
+{
+    if (!h || !h->init || h->nseries != 1) { set_error("No data has been defined."); return CF_NO_DATA_DEFINED_ERROR; }
+    CF_TRY(use_device(h));
+    if (h->end > h->begin) {
+        const size_t b = sizeof(double) * (size_t)(h->end - h->begin), o = (size_t)h->begin;
+        if (ys) CF_CUDA(cudaMemcpyAsync(ys + o, h->ys + o, b, cudaMemcpyDeviceToHost, h->stream));
+        if (rw) CF_CUDA(cudaMemcpyAsync(rw + o, h->rw + o, b, cudaMemcpyDeviceToHost, h->stream));
+        if (res) CF_CUDA(cudaMemcpyAsync(res + o, h->res + o, b, cudaMemcpyDeviceToHost, h->stream));
+    }
+    CF_CUDA(cudaStreamSynchronize(h->stream));
+    return CF_OK;
+}
 
 int32_t cf_lowess_init_device(cf_lowess* h, const void* d_x, const void* d_y, int32_t n, int32_t sort)
 {
@@ -538,6 +598,13 @@ static int32_t run_passes(cf_lowess* h, int32_t passes, bool first_uses_rw, cf_s
         if (p + 1 < passes) {                                      // :696
             if ((rc = residuals_and_robust_update(h)) != CF_OK) break;   // :695, :697-713
             use_rw = true;
+            if (p + 2 == passes && h->early_rw && h->copy_stream) {
+                // m_weights are final: their download runs beside the last fit pass
+                cudaEventRecord(h->ev_copy[0], h->stream);
+                cudaStreamWaitEvent(h->copy_stream, h->ev_copy[0], 0);
+                cudaMemcpyAsync(h->early_rw, h->rw, sizeof(double) * (size_t)h->n, cudaMemcpyDeviceToHost,
+                                h->copy_stream);
+            }
         } else {
             if ((rc = launch_residuals(h)) != CF_OK) break;        // :695
         }
@@ -860,6 +927,15 @@ int32_t cf_sort_xy(const double* x, const double* y, int32_t n, double* x_sorted
     return rc;
 }
 
+// second stream + events of the overlapped copies, created on first use
+static int ensure_copy_stream(cf_lowess* h)
+{
+    if (h->copy_stream) return CF_OK;
+    CF_CUDA(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    for (auto& ev : h->ev_copy) CF_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    return CF_OK;
+}
+
 int32_t cf_lowess_smooth(const double* x_sorted, const double* y, int32_t n, double f,
                          int32_t nsteps, double* ys, double* rw, double* res)
 {
@@ -870,12 +946,44 @@ int32_t cf_lowess_smooth(const double* x_sorted, const double* y, int32_t n, dou
     if (nsteps < 0) { set_error("nsteps must be >= 0"); return CF_INVALID_INPUT_ERROR; }
     cf_lowess* h = nullptr;
     CF_TRY(pool_acquire(&h));
-    int rc = cf_lowess_init(h, x_sorted, y, n, 0);
-    if (rc == CF_OK) rc = cf_lowess_run(h, f, nsteps, nullptr);
-    if (rc == CF_OK) {
-        if (n < 2) rc = cf_lowess_fetch(h, ys, nullptr, nullptr);     // rw, res untouched (:651-654)
-        else rc = cf_lowess_fetch(h, ys, nsteps > 0 ? rw : nullptr, res);
+    int rc = CF_OK;
+    // long series: the copies are worth overlapping with the kernels (a few ms per 100 MB)
+    const bool overlap = n >= (1 << 20) && (f == f);
+    if (!overlap) {
+        rc = cf_lowess_init(h, x_sorted, y, n, 0);
+        if (rc == CF_OK) rc = cf_lowess_run(h, f, nsteps, nullptr);
+        if (rc == CF_OK) {
+            if (n < 2) rc = cf_lowess_fetch(h, ys, nullptr, nullptr);     // rw, res untouched (:651-654)
+            else rc = cf_lowess_fetch(h, ys, nsteps > 0 ? rw : nullptr, res);
+        }
+        pool_release(h, rc);
+        return rc;
     }
+    auto body = [&]() -> int {
+        CF_TRY(layout_series(h, n));                                  // ls_init, srt = .false. (:800-803)
+        CF_TRY(ensure_copy_stream(h));
+        const size_t bytes = sizeof(double) * (size_t)n;
+        CF_CUDA(cudaMemcpyAsync(h->x, x_sorted, bytes, cudaMemcpyHostToDevice, h->stream));
+        CF_CUDA(cudaEventRecord(h->ev_copy[0], h->stream));
+        // y follows x over the bus on the second stream while the window search (x only) runs
+        CF_CUDA(cudaStreamWaitEvent(h->copy_stream, h->ev_copy[0], 0));
+        CF_CUDA(cudaMemcpyAsync(h->y, y, bytes, cudaMemcpyHostToDevice, h->copy_stream));
+        CF_CUDA(cudaEventRecord(h->ev_copy[1], h->copy_stream));
+        h->win_f = -1.0;
+        CF_TRY(begin_stage(h, f));                                    // windows
+        CF_CUDA(cudaStreamWaitEvent(h->stream, h->ev_copy[1], 0));
+        h->early_rw = (rw && nsteps > 0) ? rw : nullptr;
+        int rc2 = cf_lowess_run(h, f, nsteps, nullptr);
+        h->early_rw = nullptr;
+        if (rc2 != CF_OK) { cudaStreamSynchronize(h->copy_stream); return rc2; }
+        CF_CUDA(cudaMemcpyAsync(ys, h->ys, bytes, cudaMemcpyDeviceToHost, h->stream));
+        if (res) CF_CUDA(cudaMemcpyAsync(res, h->res, bytes, cudaMemcpyDeviceToHost, h->stream));
+        CF_CUDA(cudaStreamSynchronize(h->stream));
+        CF_CUDA(cudaStreamSynchronize(h->copy_stream));
+        return CF_OK;
+    };
+    rc = body();
+    if (rc != CF_OK && h->copy_stream) cudaStreamSynchronize(h->copy_stream);
     pool_release(h, rc);
     return rc;
 }

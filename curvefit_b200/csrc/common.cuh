@@ -221,6 +221,13 @@ struct cf_lowess {
     unsigned long long peer_timeout_ns = 60000000000ull;
     unsigned long long epoch_hist = 0, epoch_bar = 0;
 
+    // cf_lowess_smooth (host buffers): second stream for copies that overlap kernels -- y's upload
+    // runs beside the window search, the download of the final robustness weights beside the
+    // last fit pass (they are final once the last robustness update is done, :704-713)
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_copy[2] = {};
+    double* early_rw = nullptr;           // host destination of that download (null: none)
+
     // counters for cf_stats
     int launches = 0, fit_launches = 0;
     bool timing = false;                  // cf_lowess_run with stats: stage events are recorded
@@ -273,6 +280,8 @@ int fp64_peak(int device, double ms_target, double* tflops, double* mhz);
 // upload elements [lo, hi] only (x outside becomes -inf / +inf sentinels)
 int layout_series(cf_lowess* h, int32_t n);
 int upload_span(cf_lowess* h, const double* x, const double* y, int32_t lo, int32_t hi);
+void shard_span_host(const double* x, int32_t n, int32_t ns, int32_t begin, int32_t end, int32_t* lo_out,
+                     int32_t* hi_out);
 const char* last_error_text();
 
 }  // namespace cf

@@ -158,15 +158,10 @@ int32_t cf_lowess_smooth_multi(const double* x_sorted, const double* y, int32_t 
         int rc = CF_OK;
         if (cudaSetDevice(h->device) != cudaSuccess) rc = CF_DEVICE_ERROR;
         h->method = method;
-        // the elements the windows of [begin, end) can reach (windows.cu reads x(L + ns) for
-        // L <= i): [begin - ns, end - 1 + ns], widened over ties -- a window with h = 0 takes
-        // every point equal to xs (:546), and the leader of a tie group may lie below
-        int64_t lo = (int64_t)h->begin - ns, hi = (int64_t)h->end - 1 + ns;
-        if (lo < 0) lo = 0;
-        if (hi > n - 1) hi = n - 1;
-        lo = std::lower_bound(x_sorted, x_sorted + lo, x_sorted[lo]) - x_sorted;
-        hi = (std::upper_bound(x_sorted + hi, x_sorted + n, x_sorted[hi]) - x_sorted) - 1;
-        if (rc == CF_OK) rc = upload_span(h, x_sorted, y, (int32_t)lo, (int32_t)hi);
+        // only the elements the windows of [begin, end) can reach (shard_span_host, api.cu)
+        int32_t lo = 0, hi = 0;
+        shard_span_host(x_sorted, n, ns, h->begin, h->end, &lo, &hi);
+        if (rc == CF_OK) rc = upload_span(h, x_sorted, y, lo, hi);
         if (rc != CF_OK) {
             fail(rc);
             std::lock_guard<std::mutex> g(bar.mu);

@@ -131,6 +131,21 @@ class DeviceStages:
         self._check(self.lib.cf_lowess_init(self.h, x.ctypes.data_as(_lib.c_dp), y.ctypes.data_as(_lib.c_dp),
                                             self.n, 0))
 
+    def upload_span(self, x: np.ndarray, y: np.ndarray, f: float) -> int:
+        """ls_init with srt = .false., uploading only the elements this rank's windows reach
+        (block + the (ns-1)-point halo either side, cf_lowess_shard_span); returns how many."""
+        assert x.size == self.n and y.size == self.n, "series length is fixed for a sharded handle"
+        first, last = C.c_int32(), C.c_int32()
+        xp, yp = x.ctypes.data_as(_lib.c_dp), y.ctypes.data_as(_lib.c_dp)
+        self._check(self.lib.cf_lowess_shard_span(self.h, xp, self.n, float(f), C.byref(first), C.byref(last)))
+        self._check(self.lib.cf_lowess_init_span(self.h, xp, yp, self.n, first.value, last.value))
+        return last.value - first.value + 1
+
+    def fetch_block(self, ys, rw, res) -> None:
+        """Own block [begin, end) of ys, rw, res -> the same positions of full-length host arrays."""
+        p = lambda a: None if a is None else a.ctypes.data_as(_lib.c_dp)
+        self._check(self.lib.cf_lowess_fetch_block(self.h, p(ys), p(rw), p(res)))
+
     def fetch(self, ys, rw, res) -> None:
         p = lambda a: None if a is None else a.ctypes.data_as(_lib.c_dp)
         self._check(self.lib.cf_lowess_fetch(self.h, p(ys), p(rw), p(res)))
@@ -227,13 +242,25 @@ class ShardedLowess:
         if int(bad.item()) != 0:
             raise RuntimeError("a peer-memory wait timed out on some rank: results are invalid")
 
-    def smooth_host(self, x: np.ndarray, y: np.ndarray, f: float, nsteps: int = 2, out=None):
-        """smooth() with HOST buffers on every call: each rank uploads the (sorted) series,
-        the ranks smooth it together, and the caller's rank(s) read ys, rw, res back.
-        `out` = (ys, rw, res) host arrays of length n, or None on ranks that do not need
-        the result.  The series length must not change while peers are attached."""
+    def smooth_host(self, x: np.ndarray, y: np.ndarray, f: float, nsteps: int = 2, out=None,
+                    shared_out: bool = False):
+        """smooth() with HOST buffers on every call.
+        shared_out = False: each rank uploads the whole (sorted) series, the ranks smooth it
+        together, and the ranks that pass `out` = (ys, rw, res) read the whole result back.
+        shared_out = True: `out` arrays live in host memory ALL ranks map (SharedHostArray):
+        each rank uploads only the elements its windows reach and writes only its own block of
+        the result; a barrier ends the call, after which every rank sees the whole result.
+        The series length must not change while peers are attached."""
         s = self.s
+        if shared_out:
+            self.last_upload = s.upload_span(x, y, f)
+            self.run(f, nsteps, gather=False)
+            s.fetch_block(*out)
+            if s.nranks > 1:
+                dist.barrier(group=self.group)
+            return out
         s.upload(x, y)
+        self.last_upload = s.n
         self.run(f, nsteps, gather=True, with_rw=nsteps > 0)
         if out is not None:
             s.fetch(*out)
@@ -263,3 +290,43 @@ class ShardedLowess:
             self.collectives += 1
             outs.append(full[: s.n])
         return outs[0], outs[1]
+
+
+class SharedHostArray:
+    """A float64 host array in POSIX shared memory that every rank of the job maps and
+    page-locks (cudaHostRegister), so that each rank's device can copy its own block of a
+    result straight into it.  Collective: rank 0 creates, the others attach."""
+
+    def __init__(self, n: int, group: Optional[dist.ProcessGroup] = None):
+        from multiprocessing import shared_memory
+        rank = dist.get_rank(group) if dist.is_initialized() else 0
+        name = [None]
+        self._shm = None
+        if rank == 0:
+            self._shm = shared_memory.SharedMemory(create=True, size=max(8 * n, 8))
+            name[0] = self._shm.name
+        if dist.is_initialized():
+            dist.broadcast_object_list(name, src=0, group=group)
+        if rank != 0:
+            self._shm = shared_memory.SharedMemory(name=name[0])
+        self.array = np.ndarray((n,), dtype=np.float64, buffer=self._shm.buf)
+        self._owner = rank == 0
+        self._registered = False
+        if torch.cuda.is_available():
+            rc = torch.cuda.cudart().cudaHostRegister(self.array.ctypes.data, 8 * n, 0)
+            self._registered = int(rc) == 0
+        if dist.is_initialized():
+            dist.barrier(group=group)
+
+    def close(self, group: Optional[dist.ProcessGroup] = None) -> None:
+        if self._shm is None:
+            return
+        if self._registered:
+            torch.cuda.cudart().cudaHostUnregister(self.array.ctypes.data)
+        self.array = None
+        if dist.is_initialized():
+            dist.barrier(group=group)
+        self._shm.close()
+        if self._owner:
+            self._shm.unlink()
+        self._shm = None

@@ -171,6 +171,20 @@ CF_API int32_t cf_lowess_init(cf_lowess* h, const double* x, const double* y,
 CF_API int32_t cf_lowess_init_device(cf_lowess* h, const void* d_x, const void* d_y,
                                      int32_t n, int32_t sort);
 
+/* ls_init with srt = .false. for a range-sharded handle that receives only the elements its
+ * shard's windows reach: x_sorted, y are the whole host series (length n), of which elements
+ * first .. last (1-based, inclusive) are uploaded; x outside becomes -inf / +inf sentinels
+ * (x(1) and x(n) keep their values: lowest() needs x(n) - x(1), :535), y outside is
+ * untouched.  cf_lowess_shard_span gives the span the handle's shard (cf_lowess_set_shard)
+ * needs for span fraction f: the shard's block plus ns elements on either side, widened over
+ * ties -- the (ns-1)-point halo.  cf_lowess_fetch_block copies only the shard's own block
+ * [begin, end) of ys, rw, res into full-length host arrays (each may be NULL). */
+CF_API int32_t cf_lowess_shard_span(const cf_lowess* h, const double* x_sorted, int32_t n, double f,
+                                    int32_t* first, int32_t* last);
+CF_API int32_t cf_lowess_init_span(cf_lowess* h, const double* x_sorted, const double* y, int32_t n,
+                                   int32_t first, int32_t last);
+CF_API int32_t cf_lowess_fetch_block(cf_lowess* h, double* ys, double* rw, double* res);
+
 /* Batched variant: nseries independent series of equal length n, row-major
  * [nseries][n], x already ascending per row (srt = .false. semantics).  Every
  * later call on the handle (run, fetch, windows) then works on all series at

@@ -170,3 +170,32 @@ def test_c_example_runs_on_the_device(tmp_path):
     r = _cc([_build_example(tmp_path)], timeout=300)
     assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
     assert "ys =" in r.stdout
+
+
+def test_cmake_build_produces_the_same_abi(tmp_path):
+    """north_star names the repo's CMake as the build: configure + build into a scratch
+    directory (sm_100a only) and check that the library exports every symbol the header
+    declares.  (build() uses the Makefile; both compile the same sources with the same flags.)"""
+    import shutil
+    import subprocess
+    cmake = shutil.which("cmake")
+    if cmake is None or shutil.which("nvcc") is None:
+        pytest.skip("cmake / nvcc not on PATH")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ)
+    env.pop("CC", None)
+    env.pop("CXX", None)
+    bdir, odir = str(tmp_path / "b"), str(tmp_path / "out")
+    subprocess.run([cmake, "-S", root, "-B", bdir, "-DCMAKE_CUDA_HOST_COMPILER=/usr/bin/g++",
+                    "-DCMAKE_CXX_COMPILER=/usr/bin/g++", f"-DCURVEFIT_OUTPUT_DIR={odir}"],
+                   check=True, env=env, capture_output=True, timeout=300)
+    subprocess.run([cmake, "--build", bdir, "-j8"], check=True, env=env, capture_output=True, timeout=900)
+    so = os.path.join(odir, "libcurvefit_cuda.so")
+    assert os.path.exists(so)
+    syms = subprocess.run(["nm", "-D", "--defined-only", so], check=True, capture_output=True, text=True).stdout
+    have = {ln.split()[-1] for ln in syms.splitlines() if ln.strip()}
+    from curvefit_b200 import _lib
+    missing = [name for name in _lib.SIGNATURES if name not in have]
+    assert not missing, missing
+    sass = subprocess.run(["cuobjdump", "-lelf", so], capture_output=True, text=True).stdout
+    assert "sm_100a" in sass and "sm_90" not in sass

@@ -116,6 +116,23 @@ class NumpyStages:
     def sync(self):
         pass
 
+    # host-buffer path (smooth_host with shared_out): only the span is "uploaded", only the block read back
+    def upload_span(self, x, y, f):
+        ns = max(min(int(f * float(self.n)), self.n), 2)
+        lo, hi = max(self.begin - ns, 0), min(self.end - 1 + ns, self.n - 1)
+        lo = int(np.searchsorted(x[:lo], x[lo], side="left")) if lo > 0 else 0
+        hi = hi + int(np.searchsorted(x[hi:], x[hi], side="right")) - 1
+        self.x = np.where((np.arange(self.n) < lo), -np.inf, np.where(np.arange(self.n) > hi, np.inf, x))
+        self.x[0], self.x[-1] = x[0], x[-1]
+        self.y = np.where((np.arange(self.n) >= lo) & (np.arange(self.n) <= hi), y, np.nan)
+        return hi - lo + 1
+
+    def fetch_block(self, ys, rw, res):
+        b, e = self.begin, self.end
+        ys[b:e] = self.ys.numpy()[b:e]
+        rw[b:e] = self.rw.numpy()[b:e]
+        res[b:e] = self.res.numpy()[b:e]
+
 
 def _worker(rank, world, port, n, f, nsteps, kind, q):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
@@ -175,3 +192,51 @@ def test_partition_is_tile_aligned_and_covers_everything():
         for (b0, e0), (b1, e1) in zip(parts, parts[1:]):
             assert e0 == b1 and b0 <= e0
         assert all(b % 512 == 0 or b == n for b, _ in parts)
+
+
+def _worker_host(rank, world, port, n, f, nsteps, q):
+    from curvefit_b200.distributed import SharedHostArray
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        x = cases.make_x("uniform", n, 5)
+        y = cases.make_y(x, 5)
+        outs = [SharedHostArray(n) for _ in range(3)]
+        for o in outs:
+            if rank == 0:
+                o.array[:] = np.nan
+        dist.barrier()
+        job = ShardedLowess(NumpyStages(x.copy(), y.copy(), rank, world))
+        job.smooth_host(x, y, f, nsteps, tuple(o.array for o in outs), shared_out=True)
+        # every rank sees the whole result although each wrote only its block
+        q.put((rank, [o.array.copy() for o in outs], job.last_upload))
+        for o in outs:
+            o.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_smooth_host_shared_output_uploads_halo_only_and_assembles_blocks(oracle):
+    """world_size 2 over gloo: each rank receives only its block + halo (the rest of x is
+    +-inf, of y NaN -- the oracle stand-in would propagate them if a window reached there)
+    and writes only its own block of the shared result."""
+    world, n, f, nsteps = 2, 3000, 0.1, 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_host, args=(r, world, port, n, f, nsteps, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    outs = [q.get(timeout=180) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    x = cases.make_x("uniform", n, 5)
+    y = cases.make_y(x, 5)
+    ref = oracle.lowess(x, y, f, nsteps)
+    for rank, (ys, rw, res), uploaded in outs:
+        assert np.array_equal(ys, ref["ys"]), rank
+        assert np.array_equal(res, ref["res"]), rank
+        assert np.array_equal(rw, ref["rw"]), rank
+        assert uploaded < n                   # halo-limited, not the whole series

@@ -5,6 +5,7 @@ reference's own LOWESS test asserts nothing
 (/root/reference tests/curvefit_test_regression.f90:10-48), so these stand in
 for goldens (PARITY UNPINNED, see oracle header)."""
 import os
+import sys
 
 import numpy as np
 import pytest
@@ -226,3 +227,39 @@ def test_oracle_reproduces_the_published_netlib_example(oracle, nsteps, delta):
 def test_python_transliteration_reproduces_the_published_netlib_example(nsteps, delta):
     ys = py_lowess.lowess(cases.NETLIB_X, cases.NETLIB_Y, cases.NETLIB_F, nsteps, delta)[0]
     assert np.array_equal(np.round(np.asarray(ys, dtype=np.float64), 3), np.array(cases.NETLIB_YS[(nsteps, delta)]))
+
+
+# ---- the untouched reference, wherever it can be built (oracle/ref/build_ref.sh) -----------------
+def _ref_dump(name):
+    import struct
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref",
+                        f"out_{name}.bin")
+    if not os.path.exists(path):
+        return None
+    raw = open(path, "rb").read()
+    (n,) = struct.unpack("<i", raw[:4])
+    a = np.frombuffer(raw, dtype="<f8", offset=4, count=4 * n).reshape(4, n)
+    return {"xs": a[0], "ysrt": a[1], "ys": a[2], "res": a[3]}
+
+
+@pytest.mark.parametrize("name", ["c1_f02", "c1_f08", "n4096_uniform", "n1000_ties", "n1500_clustered_srt"])
+def test_oracle_matches_reference_dumps(oracle, name):
+    """Pins the oracle on the reference ITSELF: smooth() of the untouched Fortran, built by
+    oracle/ref/build_ref.sh and run on the inputs of tests/golden/make_ref_inputs.py.  Skips
+    where no Fortran compiler has produced the dumps (this image, the B200 boxes): until it
+    has run somewhere, parity stays 'unpinned' (DESIGN.md section 5)."""
+    ref = _ref_dump(name)
+    if ref is None:
+        pytest.skip("oracle/_ref has no dump of the reference (no Fortran compiler here)")
+    sys.path.insert(0, os.path.join(os.path.dirname(__file__), "golden"))
+    import make_ref_inputs
+    x, y, f, srt = make_ref_inputs.make(name)
+    if srt:
+        xs, ysrt = oracle.ls_init(x, y)
+        assert np.array_equal(xs, ref["xs"])
+        assert np.array_equal(ysrt, ref["ysrt"])          # same quicksort, same tie permutation
+    else:
+        xs, ysrt = x, y
+    got = oracle.lowess(xs, ysrt, f, 2)
+    assert np.array_equal(got["ys"], ref["ys"])
+    assert np.array_equal(got["res"], ref["res"])
