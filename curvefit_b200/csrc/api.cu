@@ -15,9 +15,17 @@
 #include <new>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>      // header-only: ranges cost nothing unless a profiler is attached
+
 #include "common.cuh"
 
 namespace cf {
+
+// NVTX range over a host-side stage (launch sequence) of the lowess driver loop
+struct NvtxRange {
+    explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+};
 
 static thread_local char g_err[512] = "";
 
@@ -155,6 +163,7 @@ static int begin_stage(cf_lowess* h, double f)
         h->win_f = -1.0;                   // windows are per fitted point
     }
     if (h->n >= 2 && (h->win_f != f || h->ns != ns)) {
+        NvtxRange r("windows");
         h->ns = ns;
         CF_TRY(launch_windows(h, ns));
         h->win_f = f;
@@ -591,10 +600,15 @@ static int32_t run_passes(cf_lowess* h, int32_t passes, bool first_uses_rw, cf_s
     int rc = CF_OK;
     bool use_rw = first_uses_rw;
     h->timing = timed;
+    NvtxRange whole("cf_lowess passes");
     for (int32_t p = 0; p < passes && rc == CF_OK; ++p) {          // :657
         if ((rc = mark()) != CF_OK) break;
-        if ((rc = launch_fit(h, use_rw)) != CF_OK) break;          // :662-693
+        {
+            NvtxRange r(use_rw ? "lowest pass (robustness weights)" : "lowest pass (first)");
+            if ((rc = launch_fit(h, use_rw)) != CF_OK) break;      // :662-693
+        }
         if ((rc = mark()) != CF_OK) break;
+        NvtxRange r2(p + 1 < passes ? "residuals + median + bisquare" : "residuals");
         if (p + 1 < passes) {                                      // :696
             if ((rc = residuals_and_robust_update(h)) != CF_OK) break;   // :695, :697-713
             use_rw = true;

@@ -285,38 +285,59 @@ pick0_kernel(SelectState* st, unsigned int* hist0, int32_t ntotal, SelGeom g)
 }
 
 // ---- pass B: the keys of the bucket(s) holding the tracked ranks ----------------------------
+// 1-3 % of the elements are candidates.  They are collected per CTA in shared memory (shared
+// atomics) and appended to the list with ONE global atomic per flush: a global atomic per warp
+// and trip on the single counter st->ncand serialised in L2 (n = 1e8: 1.47 ms for a pass whose
+// 0.8 GB read takes 0.13 ms).
+constexpr int kCompactThreads = 512, kCompactU = 4, kCompactBuf = 5120;
 template <int SRC>
-__global__ void __launch_bounds__(512)
+__global__ void __launch_bounds__(kCompactThreads)
 compact_kernel(const double* __restrict__ src, int32_t begin, int32_t end, int32_t n, SelGeom g,
                SelectState* st, unsigned long long* __restrict__ cand, int64_t cand_stride,
                int64_t cand_base)
 {
+    __shared__ unsigned long long buf[kCompactBuf];
+    __shared__ unsigned int cnt_sh, base_sh;
     src += (size_t)blockIdx.y * (size_t)n;
     st += blockIdx.y;
     cand += (size_t)blockIdx.y * (size_t)cand_stride + (size_t)cand_base;
     const int shift0 = g.top - g.b0;
     const unsigned b0 = st->bucket[0], b1 = st->bucket[1];
-    const int lane = threadIdx.x & 31;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     const int64_t cnt = (int64_t)end - begin;
-    const int64_t rounded = (cnt + 31) / 32 * 32;          // whole warps stay in the loop together
-    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < rounded; k += stride) {
-        bool take = false;
-        unsigned long long key = 0ull;
-        if (k < cnt) {
-            const double v = src[begin + k];
-            key = SRC == kSrcOrdered ? ordered_key(v) : abs_key(v);
+    if (threadIdx.x == 0) cnt_sh = 0u;
+    __syncthreads();
+    auto flush = [&]() {                                     // all threads; cnt_sh is stable here
+        const unsigned c = cnt_sh;
+        if (threadIdx.x == 0) base_sh = c ? atomicAdd(&st->ncand, c) : 0u;
+        __syncthreads();
+        const unsigned base = base_sh;
+        for (unsigned k = threadIdx.x; k < c; k += blockDim.x) cand[base + k] = buf[k];
+        __syncthreads();
+        if (threadIdx.x == 0) cnt_sh = 0u;
+        __syncthreads();
+    };
+    // every thread of the CTA makes the same number of trips (the flush is a CTA-wide decision)
+    const int64_t first = (int64_t)blockIdx.x * blockDim.x;
+    for (int64_t k0 = first; k0 < cnt; k0 += kCompactU * stride) {
+        double v[kCompactU];
+        bool ok[kCompactU];
+#pragma unroll
+        for (int u = 0; u < kCompactU; ++u) {
+            const int64_t k = k0 + threadIdx.x + u * stride;
+            ok[u] = k < cnt;
+            v[u] = ok[u] ? src[begin + k] : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < kCompactU; ++u) {
+            const unsigned long long key = SRC == kSrcOrdered ? ordered_key(v[u]) : abs_key(v[u]);
             const unsigned b = (unsigned)(key >> shift0);
-            take = (b == b0) || (b == b1);
+            if (ok[u] && (b == b0 || b == b1)) buf[atomicAdd(&cnt_sh, 1u)] = key;
         }
-        const unsigned m = __ballot_sync(kFullMask, take);
-        if (m) {
-            unsigned base = 0;
-            if (lane == (__ffs(m) - 1)) base = atomicAdd(&st->ncand, (unsigned)__popc(m));
-            base = __shfl_sync(kFullMask, base, __ffs(m) - 1);
-            if (take) cand[base + __popc(m & ((1u << lane) - 1u))] = key;
-        }
+        __syncthreads();
+        if (cnt_sh > kCompactBuf - kCompactU * kCompactThreads) flush();
     }
+    flush();
 }
 
 // ---- pass C: one more digit, over the candidates only ------------------------------------------
@@ -444,11 +465,11 @@ int launch_compact(cf_lowess* h)
     CF_TRY(ensure_cand(h));
     const int64_t cnt = h->end > h->begin ? h->end - h->begin : 0;
     if (cnt > 0) {
-        int64_t b = (cnt + 512 * 8 - 1) / (512 * 8);
+        int64_t b = (cnt + kCompactThreads * 8 - 1) / (kCompactThreads * 8);
         const int cap = h->nseries > 1 ? 16 : 148 * 4;
         if (b > cap) b = cap;
         const int64_t base = h->nranks > 1 ? (int64_t)h->rank * h->block : 0;
-        compact_kernel<kSrcAbs><<<dim3((int)b, h->nseries), 512, 0, h->stream>>>(
+        compact_kernel<kSrcAbs><<<dim3((int)b, h->nseries), kCompactThreads, 0, h->stream>>>(
             h->res, h->begin, h->end, h->n, g, h->sel, h->cand, h->cand_stride, base);
         CF_CUDA(cudaGetLastError());
         h->launches++;

@@ -33,6 +33,9 @@ module curvefit_regression_cuda
 
     !> Code libcurvefit_cuda returns for a CUDA failure (no reference equivalent).
     integer(int32), parameter :: CF_DEVICE_ERROR = 303
+    !> Series at least this long are smoothed on all GPUs of the box
+    !! (cf_lowess_smooth_multi); shorter ones on the current device.
+    integer(int32), parameter :: CF_MULTI_GPU_MIN_POINTS = 4000000
 
     type lowess_smoothing
         private
@@ -69,6 +72,22 @@ module curvefit_regression_cuda
             integer(c_int32_t), value :: n
             real(c_double), value :: f
             integer(c_int32_t), value :: nsteps
+            real(c_double), intent(out) :: ys(*), rw(*), res(*)
+            integer(c_int32_t) :: rc
+        end function
+
+        ! one series over all (or the listed) GPUs of the box from this one process;
+        ! devices = c_null_ptr, ndev = 0: every visible device.  Falls back to one GPU
+        ! for short series or a single device (include/curvefit_cuda.h).
+        function cf_lowess_smooth_multi(x, y, n, f, nsteps, devices, ndev, ys, rw, res) &
+                bind(C, name = "cf_lowess_smooth_multi") result(rc)
+            import :: c_int32_t, c_double, c_ptr
+            real(c_double), intent(in) :: x(*), y(*)
+            integer(c_int32_t), value :: n
+            real(c_double), value :: f
+            integer(c_int32_t), value :: nsteps
+            type(c_ptr), value :: devices
+            integer(c_int32_t), value :: ndev
             real(c_double), intent(out) :: ys(*), rw(*), res(*)
             integer(c_int32_t) :: rc
         end function
@@ -256,9 +275,16 @@ contains
                 "Insufficient memory available.", CF_OUT_OF_MEMORY_ERROR)
             return
         end if
-        ! lowess(m_x, m_y, f, 2, m_delta = 0, ys, m_weights, m_residuals), :866
-        rc = cf_lowess_smooth(this%m_x, this%m_y, n, f, 2_int32, ys, &
-            this%m_weights, this%m_residuals)
+        ! lowess(m_x, m_y, f, 2, m_delta = 0, ys, m_weights, m_residuals), :866 --
+        ! range-sharded over every GPU of the box when the series is long enough to be
+        ! worth it (same results: per-point sums never cross devices), else on one
+        if (n >= CF_MULTI_GPU_MIN_POINTS) then
+            rc = cf_lowess_smooth_multi(this%m_x, this%m_y, n, f, 2_int32, &
+                c_null_ptr, 0_int32, ys, this%m_weights, this%m_residuals)
+        else
+            rc = cf_lowess_smooth(this%m_x, this%m_y, n, f, 2_int32, ys, &
+                this%m_weights, this%m_residuals)
+        end if
         if (rc /= 0) call report(errmgr, "ls_smooth", rc)
     end function
 

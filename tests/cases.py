@@ -43,6 +43,11 @@ def close(a, b, tol=1e-10):
     return point and norm, float(d.max(initial=0.0))
 
 
+# every use of the extended-precision referee below: (test id, n, refereed points) -- printed in
+# the pytest summary (tests/conftest.py) so that nobody has to guess how often it fires
+REFEREE_LOG = []
+
+
 def close_or_exact(got, ref, x, y, rw, f, tol=1e-10, max_referee=64, idx=None):
     """close(); where single points miss the pointwise bound, the extended-precision
     evaluation of the reference's own formula (py_lowess.lowest_extended, with the
@@ -58,6 +63,9 @@ def close_or_exact(got, ref, x, y, rw, f, tol=1e-10, max_referee=64, idx=None):
     if not d.max(initial=0.0) <= tol * scale + 1e-300:
         return False, float(d.max(initial=0.0)), 0
     bad = np.nonzero(d > tol * np.maximum(np.abs(ref), 1e-3 * scale) + 1e-300)[0]
+    if bad.size:
+        import os
+        REFEREE_LOG.append((os.environ.get("PYTEST_CURRENT_TEST", "?"), int(x.size), int(bad.size)))
     if bad.size > max_referee:
         return False, float(d.max(initial=0.0)), int(bad.size)
     n = x.size

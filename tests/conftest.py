@@ -17,3 +17,14 @@ def oracle():
     from oracle import oracle as o
     o.build()
     return o
+
+
+def pytest_terminal_summary(terminalreporter):
+    """How often the extended-precision referee of tests/cases.close_or_exact decided a point."""
+    from tests import cases
+    if not cases.REFEREE_LOG:
+        terminalreporter.write_line("referee (cases.close_or_exact): never used")
+        return
+    terminalreporter.write_line(f"referee (cases.close_or_exact) used in {len(cases.REFEREE_LOG)} check(s):")
+    for test, n, k in cases.REFEREE_LOG:
+        terminalreporter.write_line(f"  {k} point(s) of n = {n}: {test}")

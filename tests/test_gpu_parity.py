@@ -78,6 +78,8 @@ def test_smooth_matches_oracle(cf, oracle, kind, n, f, nsteps):
     # pointwise 1e-10 against the oracle; points where the oracle's OWN rounding exceeds
     # that (zero crossings at n >= 16384) are refereed in extended precision
     ok, d, nref = cases.close_or_exact(ys, ref["ys"], x, y, fit.m_weights if nsteps > 0 else None, f, TOL)
+    if x.size < 16384:
+        assert nref == 0, f"{nref} point(s) needed the referee at n = {x.size}"
     assert ok, ("ys", d, nref)
     # res = y - ys carries the ABSOLUTE error of ys, so its scale is y's, not its own
     d = float(np.max(np.abs(fit.m_residuals - ref["res"])))

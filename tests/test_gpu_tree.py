@@ -41,6 +41,8 @@ def test_tree_smooth_matches_oracle(cf, oracle, kind, n, f, nsteps):
     # pointwise 1e-10 against the oracle; the few points (zero crossings at n >= 16384)
     # where the oracle's OWN rounding exceeds that are refereed in extended precision
     ok, d, nref = cases.close_or_exact(ys, ref["ys"], x, y, fit.m_weights if nsteps > 0 else None, f, TOL)
+    if x.size < 16384:
+        assert nref == 0, f"{nref} point(s) needed the referee at n = {x.size}"
     assert ok, ("ys", d, nref)
     d = float(np.max(np.abs(fit.m_residuals - ref["res"])))
     assert d <= TOL * max(float(np.max(np.abs(y))), 1e-300), ("res", d)
