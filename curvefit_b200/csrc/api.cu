@@ -169,6 +169,10 @@ static int begin_stage(cf_lowess* h, double f)
         h->win_f = f;
     }
     h->ns = ns;
+    if (h->y_pending) {                    // upload_span: y arrives on the copy stream
+        CF_CUDA(cudaStreamWaitEvent(h->stream, h->ev_copy[1], 0));
+        h->y_pending = false;
+    }
     return CF_OK;
 }
 
@@ -322,6 +326,15 @@ int32_t cf_lowess_init(cf_lowess* h, const double* x, const double* y, int32_t n
 
 namespace cf {
 
+// second stream + events of the overlapped copies, created on first use
+int ensure_copy_stream(cf_lowess* h)
+{
+    if (h->copy_stream) return CF_OK;
+    CF_CUDA(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    for (auto& ev : h->ev_copy) CF_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    return CF_OK;
+}
+
 // ls_init's allocation part (:758-789) for a series of n points, nothing uploaded yet
 // (multi.cu: a rank of cf_lowess_smooth_multi receives only the elements its windows reach).
 int layout_series(cf_lowess* h, int32_t n)
@@ -368,8 +381,15 @@ int upload_span(cf_lowess* h, const double* x, const double* y, int32_t lo, int3
     h->win_f = -1.0;                                   // new data: new neighbourhoods
     h->delta_built = -1.0;
     const size_t bytes = sizeof(double) * (size_t)(hi - lo + 1);
+    CF_TRY(ensure_copy_stream(h));
     CF_CUDA(cudaMemcpyAsync(h->x + lo, x + lo, bytes, cudaMemcpyHostToDevice, h->stream));
-    CF_CUDA(cudaMemcpyAsync(h->y + lo, y + lo, bytes, cudaMemcpyHostToDevice, h->stream));
+    // y follows x over the bus on the second stream while the window search (x only) runs;
+    // the first fit pass waits for it (begin_stage)
+    CF_CUDA(cudaEventRecord(h->ev_copy[0], h->stream));
+    CF_CUDA(cudaStreamWaitEvent(h->copy_stream, h->ev_copy[0], 0));
+    CF_CUDA(cudaMemcpyAsync(h->y + lo, y + lo, bytes, cudaMemcpyHostToDevice, h->copy_stream));
+    CF_CUDA(cudaEventRecord(h->ev_copy[1], h->copy_stream));
+    h->y_pending = true;
     if (lo > 0) CF_CUDA(cudaMemcpyAsync(h->x, x, sizeof(double), cudaMemcpyHostToDevice, h->stream));
     if (hi < h->n - 1)
         CF_CUDA(cudaMemcpyAsync(h->x + (h->n - 1), x + (h->n - 1), sizeof(double), cudaMemcpyHostToDevice, h->stream));
@@ -428,6 +448,15 @@ int32_t cf_lowess_init_span(cf_lowess* h, const double* x_sorted, const double* 
     return upload_span(h, x_sorted, y, first - 1, last - 1);
 }
 
+int32_t cf_lowess_set_early_weights(cf_lowess* h, double* rw_host)
+{
+    if (!h) { set_error("null handle"); return CF_INVALID_INPUT_ERROR; }
+    CF_TRY(use_device(h));
+    if (rw_host) CF_TRY(ensure_copy_stream(h));
+    h->early_rw = rw_host;
+    return CF_OK;
+}
+
 int32_t cf_lowess_fetch_block(cf_lowess* h, double* ys, double* rw, double* res)
 {
     if (!h || !h->init || h->nseries != 1) { set_error("No data has been defined."); return CF_NO_DATA_DEFINED_ERROR; }
@@ -439,6 +468,7 @@ int32_t cf_lowess_fetch_block(cf_lowess* h, double* ys, double* rw, double* res)
         if (res) CF_CUDA(cudaMemcpyAsync(res + o, h->res + o, b, cudaMemcpyDeviceToHost, h->stream));
     }
     CF_CUDA(cudaStreamSynchronize(h->stream));
+    if (h->copy_stream) CF_CUDA(cudaStreamSynchronize(h->copy_stream));   // an early weights download
     return CF_OK;
 }
 
@@ -616,7 +646,8 @@ static int32_t run_passes(cf_lowess* h, int32_t passes, bool first_uses_rw, cf_s
                 // m_weights are final: their download runs beside the last fit pass
                 cudaEventRecord(h->ev_copy[0], h->stream);
                 cudaStreamWaitEvent(h->copy_stream, h->ev_copy[0], 0);
-                cudaMemcpyAsync(h->early_rw, h->rw, sizeof(double) * (size_t)h->n, cudaMemcpyDeviceToHost,
+                cudaMemcpyAsync(h->early_rw + h->begin, h->rw + h->begin,
+                                sizeof(double) * (size_t)(h->end - h->begin), cudaMemcpyDeviceToHost,
                                 h->copy_stream);
             }
         } else {
@@ -646,6 +677,7 @@ static int32_t run_passes(cf_lowess* h, int32_t passes, bool first_uses_rw, cf_s
         st->ms_tree_build = build;
     }
     h->timing = false;
+    h->early_rw = nullptr;                 // one-shot
     for (cudaEvent_t e : h->marks) cudaEventDestroy(e);
     h->marks.clear();
     for (cudaEvent_t e : evs) cudaEventDestroy(e);
@@ -939,15 +971,6 @@ int32_t cf_sort_xy(const double* x, const double* y, int32_t n, double* x_sorted
     cudaFree(dx); cudaFree(dy); cudaFree(ox); cudaFree(oy); cudaFree(dp);
     pool_release(h, rc);
     return rc;
-}
-
-// second stream + events of the overlapped copies, created on first use
-static int ensure_copy_stream(cf_lowess* h)
-{
-    if (h->copy_stream) return CF_OK;
-    CF_CUDA(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
-    for (auto& ev : h->ev_copy) CF_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
-    return CF_OK;
 }
 
 int32_t cf_lowess_smooth(const double* x_sorted, const double* y, int32_t n, double f,

@@ -226,7 +226,8 @@ struct cf_lowess {
     // last fit pass (they are final once the last robustness update is done, :704-713)
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t ev_copy[2] = {};
-    double* early_rw = nullptr;           // host destination of that download (null: none)
+    double* early_rw = nullptr;           // host destination of that download (null: none), full-length base
+    bool y_pending = false;               // y's upload is in flight on copy_stream (ev_copy[1])
 
     // counters for cf_stats
     int launches = 0, fit_launches = 0;
@@ -278,6 +279,7 @@ int fp64_peak(int device, double ms_target, double* tflops, double* mhz);
 
 // api.cu, used by multi.cu (cf_lowess_smooth_multi): allocate for n points without uploading;
 // upload elements [lo, hi] only (x outside becomes -inf / +inf sentinels)
+int ensure_copy_stream(cf_lowess* h);
 int layout_series(cf_lowess* h, int32_t n);
 int upload_span(cf_lowess* h, const double* x, const double* y, int32_t lo, int32_t hi);
 void shard_span_host(const double* x, int32_t n, int32_t ns, int32_t begin, int32_t end, int32_t* lo_out,

@@ -169,15 +169,15 @@ int32_t cf_lowess_smooth_multi(const double* x_sorted, const double* y, int32_t 
         }
         bar.arrive();             // nobody enters the collective run unless every rank can
         if (abort_run) return;
+        h->early_rw = (rw && nsteps > 0) ? rw : nullptr;      // leaves beside the last fit pass
         rc = cf_lowess_run(h, f, nsteps, nullptr);
         if (rc == CF_OK) {
             const size_t cnt = (size_t)(h->end - h->begin), b = sizeof(double) * cnt;
             cudaError_t e = cudaMemcpyAsync(ys + h->begin, h->ys + h->begin, b, cudaMemcpyDeviceToHost, h->stream);
-            if (e == cudaSuccess && rw && nsteps > 0)
-                e = cudaMemcpyAsync(rw + h->begin, h->rw + h->begin, b, cudaMemcpyDeviceToHost, h->stream);
             if (e == cudaSuccess && res)
                 e = cudaMemcpyAsync(res + h->begin, h->res + h->begin, b, cudaMemcpyDeviceToHost, h->stream);
             if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+            if (e == cudaSuccess && h->copy_stream) e = cudaStreamSynchronize(h->copy_stream);
             if (e != cudaSuccess) rc = cuda_fail(e, "cf_lowess_smooth_multi download", __FILE__, __LINE__);
         }
         if (rc != CF_OK) fail(rc);

@@ -141,6 +141,11 @@ class DeviceStages:
         self._check(self.lib.cf_lowess_init_span(self.h, xp, yp, self.n, first.value, last.value))
         return last.value - first.value + 1
 
+    def set_early_weights(self, rw) -> None:
+        """The next fused run copies this rank's block of the final robustness weights into the
+        full-length host array `rw` while the last fit pass runs (fetch_block completes it)."""
+        self._check(self.lib.cf_lowess_set_early_weights(self.h, None if rw is None else rw.ctypes.data_as(_lib.c_dp)))
+
     def fetch_block(self, ys, rw, res) -> None:
         """Own block [begin, end) of ys, rw, res -> the same positions of full-length host arrays."""
         p = lambda a: None if a is None else a.ctypes.data_as(_lib.c_dp)
@@ -254,8 +259,12 @@ class ShardedLowess:
         s = self.s
         if shared_out:
             self.last_upload = s.upload_span(x, y, f)
+            ys, rw, res = out
+            early = getattr(s, "p2p", False) and nsteps > 0 and rw is not None
+            if early:
+                s.set_early_weights(rw)            # leaves beside the last fit pass
             self.run(f, nsteps, gather=False)
-            s.fetch_block(*out)
+            s.fetch_block(ys, None if early else rw, res)
             if s.nranks > 1:
                 dist.barrier(group=self.group)
             return out
@@ -309,6 +318,11 @@ class SharedHostArray:
             dist.broadcast_object_list(name, src=0, group=group)
         if rank != 0:
             self._shm = shared_memory.SharedMemory(name=name[0])
+            try:        # only the creator unlinks; keep this process's tracker from trying at exit
+                from multiprocessing import resource_tracker
+                resource_tracker.unregister(self._shm._name, "shared_memory")
+            except Exception:
+                pass
         self.array = np.ndarray((n,), dtype=np.float64, buffer=self._shm.buf)
         self._owner = rank == 0
         self._registered = False

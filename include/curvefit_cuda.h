@@ -184,6 +184,12 @@ CF_API int32_t cf_lowess_shard_span(const cf_lowess* h, const double* x_sorted, 
 CF_API int32_t cf_lowess_init_span(cf_lowess* h, const double* x_sorted, const double* y, int32_t n,
                                    int32_t first, int32_t last);
 CF_API int32_t cf_lowess_fetch_block(cf_lowess* h, double* ys, double* rw, double* res);
+/* One-shot: during the NEXT cf_lowess_run the shard's block of the final robustness weights
+ * (m_weights, final once the last robustness update is done, :704-713) is copied to
+ * rw_host[begin .. end) on a second stream while the last fit pass runs; the following
+ * cf_lowess_fetch_block (pass rw = NULL there) or cf_lowess_sync completes it.  rw_host is a
+ * full-length host array; NULL cancels. */
+CF_API int32_t cf_lowess_set_early_weights(cf_lowess* h, double* rw_host);
 
 /* Batched variant: nseries independent series of equal length n, row-major
  * [nseries][n], x already ascending per row (srt = .false. semantics).  Every
