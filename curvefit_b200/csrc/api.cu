@@ -605,6 +605,41 @@ int64_t cf_lowess_launch_count(const cf_lowess* h) { return h ? (int64_t)h->laun
 // ---------------------------------------------------------------------------
 extern "C" {
 
+// The last pass of the tree evaluator in `kLastChunks` pieces of output points: the tree is built
+// once, then per piece evaluation + residuals, and the piece's ys / res leave for the host on the
+// copy stream while the next piece is evaluated (cf_lowess_smooth with host buffers: at n = 1e8
+// the 1.6 GB download takes longer than the pass).  A piece is a shard of the shard: per-point
+// sums are those of the undivided pass, bit for bit.
+constexpr int kLastChunks = 8;
+static int last_pass_chunked(cf_lowess* h, bool use_rw)
+{
+    const int32_t b0 = h->begin, e0 = h->end;
+    int64_t len = ((int64_t)(e0 - b0) + kLastChunks - 1) / kLastChunks;
+    len = (len + kTile - 1) / kTile * kTile;
+    int rc = CF_OK;
+    for (int c = 0; c < kLastChunks && rc == CF_OK; ++c) {
+        const int64_t cb = (int64_t)b0 + c * len, ce = cb + len < e0 ? cb + len : e0;
+        if (cb >= e0) break;
+        h->begin = (int32_t)cb;
+        h->end = (int32_t)ce;
+        h->tree_skip_build = c > 0;
+        rc = launch_fit(h, use_rw);
+        if (rc == CF_OK) rc = launch_residuals(h);
+        if (rc != CF_OK) break;
+        const size_t bytes = sizeof(double) * (size_t)(ce - cb);
+        cudaError_t e = cudaEventRecord(h->ev_copy[0], h->stream);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(h->copy_stream, h->ev_copy[0], 0);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(h->early_ys + cb, h->ys + cb, bytes, cudaMemcpyDeviceToHost, h->copy_stream);
+        if (e == cudaSuccess && h->early_res)
+            e = cudaMemcpyAsync(h->early_res + cb, h->res + cb, bytes, cudaMemcpyDeviceToHost, h->copy_stream);
+        if (e != cudaSuccess) rc = cuda_fail(e, "chunked last pass", __FILE__, __LINE__);
+    }
+    h->begin = b0;
+    h->end = e0;
+    h->tree_skip_build = false;
+    return rc;
+}
+
 // `passes` fit passes; the first uses rw iff first_uses_rw (lowess :657-714)
 static int32_t run_passes(cf_lowess* h, int32_t passes, bool first_uses_rw, cf_stats* st)
 {
@@ -633,6 +668,14 @@ static int32_t run_passes(cf_lowess* h, int32_t passes, bool first_uses_rw, cf_s
     NvtxRange whole("cf_lowess passes");
     for (int32_t p = 0; p < passes && rc == CF_OK; ++p) {          // :657
         if ((rc = mark()) != CF_OK) break;
+        const bool chunked = p + 1 == passes && h->early_ys && h->copy_stream && method_is_tree(h) &&
+                             h->nseries == 1 && !(h->delta > 0.0) && h->end - h->begin >= (1 << 22);
+        if (chunked) {
+            NvtxRange r("lowest pass (last, in pieces beside the download)");
+            if ((rc = last_pass_chunked(h, use_rw)) != CF_OK) break;
+            if ((rc = mark()) != CF_OK) break;
+            break;
+        }
         {
             NvtxRange r(use_rw ? "lowest pass (robustness weights)" : "lowest pass (first)");
             if ((rc = launch_fit(h, use_rw)) != CF_OK) break;      // :662-693
@@ -678,6 +721,7 @@ static int32_t run_passes(cf_lowess* h, int32_t passes, bool first_uses_rw, cf_s
     }
     h->timing = false;
     h->early_rw = nullptr;                 // one-shot
+    h->early_ys = h->early_res = nullptr;
     for (cudaEvent_t e : h->marks) cudaEventDestroy(e);
     h->marks.clear();
     for (cudaEvent_t e : evs) cudaEventDestroy(e);
@@ -1010,11 +1054,19 @@ int32_t cf_lowess_smooth(const double* x_sorted, const double* y, int32_t n, dou
         CF_TRY(begin_stage(h, f));                                    // windows
         CF_CUDA(cudaStreamWaitEvent(h->stream, h->ev_copy[1], 0));
         h->early_rw = (rw && nsteps > 0) ? rw : nullptr;
+        // tree evaluator: ys and res leave piece by piece during the last pass (run_passes)
+        h->ns = cf_lowess_span(n, f);
+        const bool pieces = method_is_tree(h) && n >= (1 << 22);
+        h->early_ys = pieces ? ys : nullptr;
+        h->early_res = pieces ? res : nullptr;
         int rc2 = cf_lowess_run(h, f, nsteps, nullptr);
         h->early_rw = nullptr;
+        h->early_ys = h->early_res = nullptr;
         if (rc2 != CF_OK) { cudaStreamSynchronize(h->copy_stream); return rc2; }
-        CF_CUDA(cudaMemcpyAsync(ys, h->ys, bytes, cudaMemcpyDeviceToHost, h->stream));
-        if (res) CF_CUDA(cudaMemcpyAsync(res, h->res, bytes, cudaMemcpyDeviceToHost, h->stream));
+        if (!pieces) {
+            CF_CUDA(cudaMemcpyAsync(ys, h->ys, bytes, cudaMemcpyDeviceToHost, h->stream));
+            if (res) CF_CUDA(cudaMemcpyAsync(res, h->res, bytes, cudaMemcpyDeviceToHost, h->stream));
+        }
         CF_CUDA(cudaStreamSynchronize(h->stream));
         CF_CUDA(cudaStreamSynchronize(h->copy_stream));
         return CF_OK;

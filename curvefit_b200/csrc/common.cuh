@@ -227,6 +227,9 @@ struct cf_lowess {
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t ev_copy[2] = {};
     double* early_rw = nullptr;           // host destination of that download (null: none), full-length base
+    double* early_ys = nullptr;           // cf_lowess_smooth: host destinations of ys / res, downloaded chunk by
+    double* early_res = nullptr;          //   chunk while the last pass of the tree evaluator is still running
+    bool tree_skip_build = false;         // tree.cu: evaluate only (the pass's tree is built)
     bool y_pending = false;               // y's upload is in flight on copy_stream (ev_copy[1])
 
     // counters for cf_stats

@@ -35,7 +35,7 @@
 // node in its own centred coordinate (so it lies wholly inside the window whenever the range
 // covers it).  A boundary path then climbs cbits[g] binary levels per node (suffix on the
 // left path, prefix on the right path); only the top, where both ends fall into one block,
-// uses binary nodes.  The launcher picks the geometry from ns (8 + 8 bits at ns = 5e6):
+// uses binary nodes.  The launcher picks the geometry from ns (one level of 16 bits at ns = 5e6):
 // n = 1e8, ns = 5e6: about 12 tricube nodes per point instead of 36.
 //
 // This backend is separate from fit.cu (the direct kernel that carries the
@@ -928,7 +928,7 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
         // Geometry: a side range holds about ns/2 elements = R leaves.  The chain levels
         // together climb T = log2(R) - 1 binary levels (so that the top units are R/2..R/4
         // leaves and what is left for the binary walk is 2-4 units), split evenly over as
-        // few levels as keep a block at <= 2^9 units.
+        // few levels as keep a block at <= 2^16 units.
         int bits[kMaxGroups + 1] = {0, 0, 0, 0, 0};
         int G = 0;
         int T = 0;
@@ -937,10 +937,14 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
         // delta > 0 with few fitted points: the chains would cost more to build than they save
         const bool sparse = h->delta > 0.0 && (int64_t)h->nfit * 64 < (int64_t)h->n;
         if (T >= 3 && !sparse) {
-            G = (T + 8) / 9;
+            // one chain level of up to 16 bits (measured at n = 1e8, ns = 5e6: 16 -> 118.9 ms per
+            // smooth, 8 + 8 -> 120.0, 15 -> 125.9, 12 + 4 -> 132.2: what counts is that the top
+            // units are R/2..R/4 leaves, and every further level costs two more nodes per range)
+            constexpr int kMaxBits = 16;
+            G = (T + kMaxBits - 1) / kMaxBits;
             if (G > kMaxGroups) G = kMaxGroups;
             for (int g = 1; g <= G; ++g) bits[g] = T / G + (g <= T % G ? 1 : 0);
-            for (int g = 1; g <= G; ++g) if (bits[g] > 9) bits[g] = 9;
+            for (int g = 1; g <= G; ++g) if (bits[g] > kMaxBits) bits[g] = kMaxBits;
         }
         if (const char* v = dev_env("CF_TREE_BITS")) {        // development: "8,8" etc.
             G = 0;
@@ -981,56 +985,57 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
         h->marks.push_back(e);
     };
     mark();
-
-    // the part of the tree inside each block of 2^cb leaves in one launch (with the level-1
-    // chain when its blocks are those); CF_TREE_FUSED=0: one launch per level as before
-    static const bool fused = !(dev_env("CF_TREE_FUSED") && atoi(dev_env("CF_TREE_FUSED")) == 0);
-    int level = 1;
-    int g0 = 1;
-    if (fused) {
-        // the level-1 chain is built inside the block launch when its blocks are small enough to be
-        // the launch's blocks; wider chain blocks get their own launch after the binary levels
-        const bool chain = prm.ngroups >= 1 && prm.cbits[1] <= 9;
-        int cb = chain ? prm.cbits[1] : 8;
-        if (cb > L - 1) cb = L - 1;
-        // few blocks: 128 threads per block (shortest critical path); many: one warp per block
-        static const int bt_env = dev_env("CF_TREE_BLOCK") ? atoi(dev_env("CF_TREE_BLOCK")) : 0;
-        const int64_t leaves = (int64_t)prm.cnt[0] * h->nseries;
-        const int bt = bt_env ? bt_env : (leaves < (1 << 20) ? 128 : 32);
-        const dim3 bg((prm.cnt[0] + (1 << cb) - 1) >> cb, h->nseries);
-        int seg = bt == 128 ? 8 : 16;                            // units per chain task
-        if (seg > (1 << cb)) seg = 1 << cb;
-        if (bt == 128) tree_block_kernel<128><<<bg, 128, 0, h->stream>>>(prm, cb, chain, seg);
-        else           tree_block_kernel<32><<<bg, 32, 0, h->stream>>>(prm, cb, chain, seg);
-        CF_CUDA(cudaGetLastError());
-        h->launches++;
-        level = cb + 1;
-        if (chain) g0 = 2;
-    } else {
-        tree_leaf_kernel<<<dim3((prm.cnt[0] + 127) / 128, h->nseries), 128, 0, h->stream>>>(prm);
-        CF_CUDA(cudaGetLastError());
-        h->launches++;
-    }
-    for (; level < L && prm.cnt[level] > 2048; ++level) {
-        tree_merge_kernel<<<dim3((prm.cnt[level] + 127) / 128, h->nseries), 128, 0, h->stream>>>(prm, level);
-        CF_CUDA(cudaGetLastError());
-        h->launches++;
-    }
-    if (level < L) {
-        tree_top_kernel<<<h->nseries, 256, 0, h->stream>>>(prm, level);
-        CF_CUDA(cudaGetLastError());
-        h->launches++;
-    }
-    for (int g = g0; g <= prm.ngroups; ++g) {
-        const int32_t ucnt = prm.cnt[prm.ulev[g]];
-        const int32_t seg = (1 << prm.cbits[g]) < kChainSeg ? (1 << prm.cbits[g]) : kChainSeg;
-        const int32_t nseg = (ucnt + seg - 1) / seg;
-        if ((int64_t)nseg * h->nseries >= 65536)      // enough segments to fill the GPU: 1 merge per entry
-            tree_chain_kernel<<<dim3((2 * nseg + 127) / 128, h->nseries), 128, 0, h->stream>>>(prm, g);
-        else                                          // short critical path instead
-            tree_chain_entry_kernel<<<dim3((2 * ucnt + 127) / 128, h->nseries), 128, 0, h->stream>>>(prm, g);
-        CF_CUDA(cudaGetLastError());
-        h->launches++;
+    if (!h->tree_skip_build) {     // api.cu's chunked last pass: the tree of this pass is already built
+        // the part of the tree inside each block of 2^cb leaves in one launch (with the level-1
+        // chain when its blocks are those); CF_TREE_FUSED=0: one launch per level as before
+        static const bool fused = !(dev_env("CF_TREE_FUSED") && atoi(dev_env("CF_TREE_FUSED")) == 0);
+        int level = 1;
+        int g0 = 1;
+        if (fused) {
+            // the level-1 chain is built inside the block launch when its blocks are small enough to be
+            // the launch's blocks; wider chain blocks get their own launch after the binary levels
+            const bool chain = prm.ngroups >= 1 && prm.cbits[1] <= 9;
+            int cb = chain ? prm.cbits[1] : 8;
+            if (cb > L - 1) cb = L - 1;
+            // few blocks: 128 threads per block (shortest critical path); many: one warp per block
+            static const int bt_env = dev_env("CF_TREE_BLOCK") ? atoi(dev_env("CF_TREE_BLOCK")) : 0;
+            const int64_t leaves = (int64_t)prm.cnt[0] * h->nseries;
+            const int bt = bt_env ? bt_env : (leaves < (1 << 20) ? 128 : 32);
+            const dim3 bg((prm.cnt[0] + (1 << cb) - 1) >> cb, h->nseries);
+            int seg = bt == 128 ? 8 : 16;                            // units per chain task
+            if (seg > (1 << cb)) seg = 1 << cb;
+            if (bt == 128) tree_block_kernel<128><<<bg, 128, 0, h->stream>>>(prm, cb, chain, seg);
+            else           tree_block_kernel<32><<<bg, 32, 0, h->stream>>>(prm, cb, chain, seg);
+            CF_CUDA(cudaGetLastError());
+            h->launches++;
+            level = cb + 1;
+            if (chain) g0 = 2;
+        } else {
+            tree_leaf_kernel<<<dim3((prm.cnt[0] + 127) / 128, h->nseries), 128, 0, h->stream>>>(prm);
+            CF_CUDA(cudaGetLastError());
+            h->launches++;
+        }
+        for (; level < L && prm.cnt[level] > 2048; ++level) {
+            tree_merge_kernel<<<dim3((prm.cnt[level] + 127) / 128, h->nseries), 128, 0, h->stream>>>(prm, level);
+            CF_CUDA(cudaGetLastError());
+            h->launches++;
+        }
+        if (level < L) {
+            tree_top_kernel<<<h->nseries, 256, 0, h->stream>>>(prm, level);
+            CF_CUDA(cudaGetLastError());
+            h->launches++;
+        }
+        for (int g = g0; g <= prm.ngroups; ++g) {
+            const int32_t ucnt = prm.cnt[prm.ulev[g]];
+            const int32_t seg = (1 << prm.cbits[g]) < kChainSeg ? (1 << prm.cbits[g]) : kChainSeg;
+            const int32_t nseg = (ucnt + seg - 1) / seg;
+            if ((int64_t)nseg * h->nseries >= 65536)      // enough segments to fill the GPU: 1 merge per entry
+                tree_chain_kernel<<<dim3((2 * nseg + 127) / 128, h->nseries), 128, 0, h->stream>>>(prm, g);
+            else                                          // short critical path instead
+                tree_chain_entry_kernel<<<dim3((2 * ucnt + 127) / 128, h->nseries), 128, 0, h->stream>>>(prm, g);
+            CF_CUDA(cudaGetLastError());
+            h->launches++;
+        }
     }
     mark();
     const int cntp = prm.end - prm.begin;

@@ -217,3 +217,29 @@ def test_windows_guided_searches_large_irregular(cf, kind):
     assert np.all((r9 == i) | inside(r9, h9)) and np.all((r9 == n - 1) | ~inside(r9 + 1, h9))
     assert np.all((l1 == i) | inside(l1, h1)) and np.all((l1 == l9) | ~inside(l1 - 1, h1))
     assert np.all((r1 == i) | inside(r1, h1)) and np.all((r1 == r9) | ~inside(r1 + 1, h1))
+
+
+@pytest.mark.parametrize("kind", ["grid", "ties"])
+def test_host_buffer_smooth_with_overlapped_copies_equals_resident_run(cf, kind):
+    """cf_lowess_smooth on a long series overlaps its copies with the kernels (y's upload beside
+    the window search, the final weights' download beside the last pass, and -- tree evaluator --
+    ys / res piece by piece during the last pass, which is then evaluated in pieces).  Every
+    output must equal the plain sequence init -> run -> fetch bit for bit, with both evaluators."""
+    n, f, nsteps = 6_000_000, 0.002, 2
+    x = datagen.grid_x(n) if kind == "grid" else np.sort(np.round(datagen.random_x(n, 9) * (n // 6)) / (n // 6))
+    y = datagen.noisy_y(x, 9)
+    for method in ("tree", "direct"):
+        fit = cf.lowess_smoothing()
+        fit.set_method(method)
+        fit.initialize(x, y, srt=False)
+        ys0 = fit.smooth(f, nsteps=nsteps)
+        rw0, res0 = fit.m_weights.copy(), fit.m_residuals.copy()
+        fit.close()
+        cf.set_default_method(method)
+        try:
+            ys1, rw1, res1 = cf.cf_lowess_smooth(x, y, f, nsteps)
+        finally:
+            cf.set_default_method("direct")
+        assert np.array_equal(ys1, ys0), method
+        assert np.array_equal(res1, res0), method
+        assert np.array_equal(rw1, rw0), method
