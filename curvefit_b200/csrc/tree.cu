@@ -70,7 +70,14 @@ struct TreeParams {
     int32_t cbits[kMaxGroups + 1];   // chain level g groups 2^cbits[g] units into a block
     int32_t ulev[kMaxGroups + 2];    // its units are the binary nodes of level ulev[g]; ulev[g+1] = ulev[g] + cbits[g]
     int64_t coff[kMaxGroups + 1];    // coff[g]: first SUF_g node; PRE_g follows after cnt[ulev[g]] nodes
+    // core prefix sums (see build_core_prefix): per leaf kQLen doubles, per block of 2^qbits leaves a
+    // header (centre, half-width); qbits == 0: not built
+    double* qsum;
+    double* qhdr;
+    int32_t qbits;
 };
+
+constexpr int kQLen = 6;             // A0, A1, A2, B0, B1, pad
 
 __device__ __forceinline__ double2 ld2(const double* p)
 {
@@ -399,6 +406,81 @@ tree_chain_kernel(const TreeParams prm, int g)
     if ((tid >> 1) < nseg) chain_segment(prm, g, blockIdx.y, seg, tid >> 1, tid & 1);
 }
 
+// ---- build: core prefix sums ------------------------------------------------------------------
+// The w = 1 core [lo1, hi1] (:547-551) holds ~0.1 % of the window but its whole leaves are a range of
+// their own: at ns = 5e6 a dozen binary nodes per point, each a step of the walk -- 19 % of the
+// evaluator's time for a sum that only needs the moments A0..A2, B0, B1.  Per block of 2^qbits
+// leaves (the block of tree_block_kernel) and leaf t the inclusive prefix Q[t] of those five
+// moments over the block's leaves up to t is kept in the BLOCK's centred coordinate; the core's
+// whole leaves inside one block are then Q[t1 - 1] - Q[t0 - 1]: two 48-byte loads instead of a walk.
+// Leaves the shard's windows cannot reach count as empty (their nodes are not built).
+// Called by the first warp of the block's CTA after the leaves are built.
+__device__ __forceinline__ void build_core_prefix(const TreeParams& prm, int series, int32_t blk0,
+                                                  int32_t blk1, int cb)
+{
+    constexpr unsigned kFull = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const double* __restrict__ x = prm.x + (size_t)series * (size_t)prm.n;
+    const double* base = prm.nodes + (size_t)series * prm.total * kNodeLen;
+    int32_t e0, e1, k0, k1;
+    node_span(0, blk0, prm.n, e0, k0);
+    node_span(0, blk1 - 1, prm.n, k1, e1);
+    const double xf = x[e0], xl = x[e1];
+    const double cB = 0.5 * xf + 0.5 * xl, dB = 0.5 * (xl - xf);
+    const double invB = dB > 0.0 ? 1.0 / dB : 0.0;
+    const int per = (1 << cb) >> 5;                               // leaves per lane (cb >= 5)
+    const int32_t first = blk0 + lane * per;
+    auto leaf_in_block = [&](int32_t leaf, double* m) -> bool {   // leaf moments in block coordinates
+        if (leaf >= blk1) return false;
+        int32_t j0, j1;
+        node_span(0, leaf, prm.n, j0, j1);
+        if (!node_needed(prm, series, j0, j1)) return false;
+        const double* nd = base + (size_t)leaf * kNodeLen;        // written by this CTA: plain loads
+        const double a = nd[1] * invB, b = (nd[0] - cB) * invB;
+        const double A0 = nd[2], A1 = nd[3], A2 = nd[4], B0 = nd[2 + kKA], B1 = nd[3 + kKA];
+        m[0] = A0;
+        m[1] = fma(b, A0, a * A1);
+        m[2] = fma(b * b, A0, fma(2.0 * a * b, A1, a * a * A2));
+        m[3] = B0;
+        m[4] = fma(b, B0, a * B1);
+        return true;
+    };
+    double tot[5] = {0.0, 0.0, 0.0, 0.0, 0.0}, m[5];
+    for (int r = 0; r < per; ++r)
+        if (leaf_in_block(first + r, m)) {
+#pragma unroll
+            for (int k = 0; k < 5; ++k) tot[k] += m[k];
+        }
+    // exclusive scan of the lane totals
+    double run[5];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+        double v = tot[k];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const double u = __shfl_up_sync(kFull, v, o);
+            if (lane >= o) v += u;
+        }
+        run[k] = v - tot[k];
+    }
+    double* q = prm.qsum + ((size_t)series * prm.cnt[0] + first) * kQLen;
+    for (int r = 0; r < per; ++r) {
+        if (first + r >= blk1) break;
+        if (leaf_in_block(first + r, m)) {
+#pragma unroll
+            for (int k = 0; k < 5; ++k) run[k] += m[k];
+        }
+        double2* o = reinterpret_cast<double2*>(q + (size_t)r * kQLen);
+        o[0] = make_double2(run[0], run[1]);
+        o[1] = make_double2(run[2], run[3]);
+        o[2] = make_double2(run[4], 0.0);
+    }
+    if (lane == 0) {
+        double2* hd = reinterpret_cast<double2*>(prm.qhdr + ((size_t)series * ((prm.cnt[0] >> cb) + 1) + (blk0 >> cb)) * 2);
+        *hd = make_double2(cB, dB);
+    }
+}
+
 // ---- build: one launch per block of leaves ------------------------------------------------
 // One CTA per block of 2^cb leaves builds everything that lives inside the block: its
 // leaves, the binary levels 1 .. cb above them and (chain != 0) the level-1 chain PRE_1 /
@@ -436,6 +518,7 @@ tree_block_kernel(const TreeParams prm, int cb, int chain, int seg)
     };
     for (int32_t leaf = blk0 + threadIdx.x; leaf < blk1; leaf += NT) build_leaf(prm, series, leaf);
     sync();
+    if (prm.qbits && threadIdx.x < 32) build_core_prefix(prm, series, blk0, blk1, cb);
     const double* __restrict__ x = prm.x + (size_t)series * (size_t)prm.n;
     double* base = prm.nodes + (size_t)series * prm.total * kNodeLen;
     for (int level = 1; level <= cb && level < prm.nlevels; ++level) {
@@ -703,9 +786,10 @@ tree_eval_kernel(const TreeParams prm)
         return v;
     };
     const double* __restrict__ nodes = prm.nodes + (size_t)blockIdx.y * prm.total * kNodeLen;
-    // PF == 2: per-warp double buffer of staged nodes (see staged_walk)
-    __shared__ __align__(16) double stage_all[PF == 2 ? (NT / 32) * 2 * kStageLen : 2];
-    double* stage = stage_all + (PF == 2 ? (threadIdx.x >> 5) * 2 * kStageLen : 0);
+    // PF >= 2: per-warp double buffer of staged nodes (see staged_walk); PF == 3: only the tricube
+    // nodes are staged, the core nodes (4 of their 13 16-byte pieces are needed) are read directly
+    __shared__ __align__(16) double stage_all[PF >= 2 ? (NT / 32) * 2 * kStageLen : 2];
+    double* stage = stage_all + (PF >= 2 ? (threadIdx.x >> 5) * 2 * kStageLen : 0);
 
     // tie followers copy their leader's value later (robust.cu); a shard that starts
     // inside a tie group fits its first point in the leader's place (as fit.cu)
@@ -766,7 +850,7 @@ tree_eval_kernel(const TreeParams prm)
             return false;
         };
         bool have = advance();
-        if (PF == 2) {
+        if (PF >= 2) {
             staged_walk(nodes, stage, have, node, advance, [&]() { return nsig; },
                         [&](const double* nd, double sg) { take_tricube<true>(nd, xs, invh, sg, m); });
         } else if (PF == 0) {
@@ -795,13 +879,40 @@ tree_eval_kernel(const TreeParams prm)
         }
     }
     // ---- phase 2: core nodes
-    {
+    if (PF != 4) {
         Chain w;
         {
             int32_t hd, tl, la = 0, lb = 0;
             if (i >= 0) {
                 const size_t pi = soff() + i;
                 split_range(ldv(prm.w.lo1 + pi), ldv(prm.w.hi1 + pi) + 1, hd, tl, la, lb);
+            }
+            // whole leaves that lie in at most three prefix blocks: differences of the blocks'
+            // core prefix sums (build_core_prefix) instead of a walk over a dozen nodes
+            const int q = prm.qbits;
+            if (q && la < lb && ((lb - 1) >> q) - (la >> q) <= 2) {
+                unsigned series;
+                asm volatile("mov.u32 %0, %%ctaid.y;" : "=r"(series));
+                const double* __restrict__ qs = prm.qsum + (size_t)series * prm.cnt[0] * kQLen;
+                const double* __restrict__ qh = prm.qhdr + (size_t)series * ((prm.cnt[0] >> q) + 1) * 2;
+                for (int32_t k = la >> q; k <= (lb - 1) >> q; ++k) {
+                    const int32_t t0 = max(la, k << q), t1 = min(lb, (k + 1) << q);
+                    const double2 cd = ld2(qh + 2 * (size_t)k);
+                    const double* hi = qs + (size_t)(t1 - 1) * kQLen;
+                    double2 a01 = ld2(hi), a2b0 = ld2(hi + 2), b1 = ld2(hi + 4);
+                    if (t0 > (k << q)) {
+                        const double* lo = qs + (size_t)(t0 - 1) * kQLen;
+                        const double2 l01 = ld2(lo), l2 = ld2(lo + 2), l4 = ld2(lo + 4);
+                        a01.x -= l01.x; a01.y -= l01.y; a2b0.x -= l2.x; a2b0.y -= l2.y; b1.x -= l4.x;
+                    }
+                    const double beta = (cd.x - xs) * invh, alpha = cd.y * invh;
+                    m.S0 += a01.x;
+                    m.S1 += fma(beta, a01.x, alpha * a01.y);
+                    m.S2 += fma(beta * beta, a01.x, fma(2.0 * alpha * beta, a01.y, alpha * alpha * a2b0.x));
+                    m.T0 += a2b0.y;
+                    m.T1 += fma(beta, a2b0.y, alpha * b1.x);
+                }
+                la = lb = 0;
             }
             w.start(la, lb);
         }
@@ -820,7 +931,7 @@ tree_eval_kernel(const TreeParams prm)
         }
     }
     // ---- phase 3: range ends, element by element (:542-556 per pair)
-    {
+    if (PF != 5) {
         // adjacent pieces are merged: [l9,hdL) | [tlL,l1)+[l1,hdC) | [tlC,r1+1)+[r1+1,hdR) | [tlR,r9+1).
         // Two independent streams per lane -- A: pieces 1, 2 (left of the core and its head),
         // B: pieces 3, 4 -- with their own accumulators, walked by ONE counter k: element k of a
@@ -966,8 +1077,20 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
         }
     }
     prm.total = total;
+    // the part of the tree inside each block of 2^cb leaves is built by one launch (with the level-1
+    // chain when its blocks are those); CF_TREE_FUSED=0 (development): one launch per level as before
+    static const bool fused = !(dev_env("CF_TREE_FUSED") && atoi(dev_env("CF_TREE_FUSED")) == 0);
+    // the level-1 chain is built inside the block launch when its blocks are small enough to be
+    // the launch's blocks; wider chain blocks get their own launch after the binary levels
+    const bool chain_in_block = prm.ngroups >= 1 && prm.cbits[1] <= 9;
+    int cb = chain_in_block ? prm.cbits[1] : 8;
+    if (cb > L - 1) cb = L - 1;
+    prm.qbits = (fused && cb >= 5) ? cb : 0;           // core prefix sums per block of that launch
+    const size_t node_doubles = kNodeLen * ((size_t)total * (size_t)h->nseries + kStage);
+    const size_t qsum_doubles = prm.qbits ? (size_t)kQLen * prm.cnt[0] * (size_t)h->nseries : 0;
+    const size_t qhdr_doubles = prm.qbits ? 2 * (size_t)((prm.cnt[0] >> prm.qbits) + 1) * (size_t)h->nseries : 0;
     // + kStage nodes: the evaluator stages kStage consecutive nodes from any index it needs
-    const size_t need = sizeof(double) * kNodeLen * ((size_t)total * (size_t)h->nseries + kStage);
+    const size_t need = sizeof(double) * (node_doubles + qsum_doubles + qhdr_doubles);
     if (need > h->tree_bytes) {
         cudaFree(h->tree);
         h->tree = nullptr;
@@ -976,6 +1099,8 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
         h->tree_bytes = need;
     }
     prm.nodes = h->tree;
+    prm.qsum = h->tree + node_doubles;
+    prm.qhdr = prm.qsum + qsum_doubles;
     prm.span = h->span;
     auto mark = [&]() {
         if (!h->timing) return;
@@ -986,17 +1111,10 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
     };
     mark();
     if (!h->tree_skip_build) {     // api.cu's chunked last pass: the tree of this pass is already built
-        // the part of the tree inside each block of 2^cb leaves in one launch (with the level-1
-        // chain when its blocks are those); CF_TREE_FUSED=0: one launch per level as before
-        static const bool fused = !(dev_env("CF_TREE_FUSED") && atoi(dev_env("CF_TREE_FUSED")) == 0);
         int level = 1;
         int g0 = 1;
         if (fused) {
-            // the level-1 chain is built inside the block launch when its blocks are small enough to be
-            // the launch's blocks; wider chain blocks get their own launch after the binary levels
-            const bool chain = prm.ngroups >= 1 && prm.cbits[1] <= 9;
-            int cb = chain ? prm.cbits[1] : 8;
-            if (cb > L - 1) cb = L - 1;
+            const bool chain = chain_in_block;
             // few blocks: 128 threads per block (shortest critical path); many: one warp per block
             static const int bt_env = dev_env("CF_TREE_BLOCK") ? atoi(dev_env("CF_TREE_BLOCK")) : 0;
             const int64_t leaves = (int64_t)prm.cnt[0] * h->nseries;
@@ -1039,10 +1157,11 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
     }
     mark();
     const int cntp = prm.end - prm.begin;
-    // 7 CTAs of 128 threads per SM (72 registers) + L1 prefetch of the next node; the
-    // others are kept for measurement (B200, n = 1e8 smooth: 5 CTAs 143.2 ms, 6: 128.6,
-    // 7: 125.7, 7 + prefetch 125.3)
-    static const int variant = dev_env("CF_TREE_EVAL") ? atoi(dev_env("CF_TREE_EVAL")) : 72;
+    // 7 CTAs of 128 threads per SM (72 registers), tricube nodes staged per warp, core nodes read
+    // directly; the others are kept for measurement in development builds (B200, n = 1e8 smooth,
+    // round 1: 5 CTAs 143.2 ms, 6: 128.6, 7: 125.7, 7 + L1 prefetch 125.3; round 2, one 16-bit
+    // chain level: staged tricube + core nodes 111.7, core nodes direct 108.9)
+    static const int variant = dev_env("CF_TREE_EVAL") ? atoi(dev_env("CF_TREE_EVAL")) : 73;
     const dim3 eg((cntp + 127) / 128, h->nseries);
     switch (variant) {
 #ifdef CF_DEVELOPMENT
@@ -1052,8 +1171,12 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
     case 71: tree_eval_kernel<128, 7, 1><<<eg, 128, 0, h->stream>>>(prm); break;   // round 1: per-lane node loads
     case 62: tree_eval_kernel<128, 6, 2><<<eg, 128, 0, h->stream>>>(prm); break;
     case 52: tree_eval_kernel<128, 5, 2><<<eg, 128, 0, h->stream>>>(prm); break;
+
+    case 72: tree_eval_kernel<128, 7, 2><<<eg, 128, 0, h->stream>>>(prm); break;   // core nodes staged too
+    case 74: tree_eval_kernel<128, 7, 4><<<eg, 128, 0, h->stream>>>(prm); break;   // accounting: phase 2 skipped (wrong results)
+    case 75: tree_eval_kernel<128, 7, 5><<<eg, 128, 0, h->stream>>>(prm); break;   // accounting: phase 3 skipped (wrong results)
 #endif
-    default: tree_eval_kernel<128, 7, 2><<<eg, 128, 0, h->stream>>>(prm); break;   // warp-staged nodes
+    default: tree_eval_kernel<128, 7, 3><<<eg, 128, 0, h->stream>>>(prm); break;   // warp-staged tricube nodes
     }
     CF_CUDA(cudaGetLastError());
     h->launches++;
