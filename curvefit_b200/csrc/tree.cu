@@ -105,6 +105,18 @@ __device__ __forceinline__ bool node_needed(const TreeParams& prm, int series, i
 }
 
 // ---- build: leaves -------------------------------------------------------------------
+// centre and half-width of prefix block k (2^qbits leaves), as stored in its header
+__device__ __forceinline__ void core_block_coord(const TreeParams& prm, const double* __restrict__ x, int32_t k,
+                                                 double& cB, double& dB)
+{
+    const int64_t e0 = ((int64_t)k << prm.qbits) * kLeaf;
+    int64_t e1 = ((int64_t)(k + 1) << prm.qbits) * kLeaf;
+    if (e1 > prm.n) e1 = prm.n;
+    const double xf = x[e0], xl = x[e1 - 1];
+    cB = 0.5 * xf + 0.5 * xl;
+    dB = 0.5 * (xl - xf);
+}
+
 __device__ __forceinline__ void build_leaf(const TreeParams& prm, int series, int32_t leaf)
 {
     const size_t soff = (size_t)series * (size_t)prm.n;
@@ -115,7 +127,13 @@ __device__ __forceinline__ void build_leaf(const TreeParams& prm, int series, in
 
     int32_t j0, j1;
     node_span(0, leaf, prm.n, j0, j1);
-    if (!node_needed(prm, series, j0, j1)) return;
+    // core prefix sums (build_core_prefix): the leaf's entry starts as its own moments A0..A2, B0,
+    // B1 in the block's coordinate -- zero for a leaf the shard's windows cannot reach
+    double2* qe = prm.qbits ? reinterpret_cast<double2*>(prm.qsum + ((size_t)series * prm.cnt[0] + leaf) * kQLen) : nullptr;
+    if (!node_needed(prm, series, j0, j1)) {
+        if (qe) { qe[0] = make_double2(0.0, 0.0); qe[1] = make_double2(0.0, 0.0); qe[2] = make_double2(0.0, 0.0); }
+        return;
+    }
     const double xf = x[j0], xl = x[j1];
     const double c = 0.5 * xf + 0.5 * xl;
     const double d = 0.5 * (xl - xf);
@@ -144,6 +162,15 @@ __device__ __forceinline__ void build_leaf(const TreeParams& prm, int series, in
 #pragma unroll
     for (int k = 0; k < 5; ++k) o[7 + k] = make_double2(Bm[2 * k], Bm[2 * k + 1]);
     o[12] = make_double2(Bm[10], 0.0);
+    if (qe) {
+        double cB, dB;
+        core_block_coord(prm, x, leaf >> prm.qbits, cB, dB);
+        const double invB = dB > 0.0 ? 1.0 / dB : 0.0;
+        const double a = d * invB, b = (c - cB) * invB;
+        qe[0] = make_double2(A[0], fma(b, A[0], a * A[1]));
+        qe[1] = make_double2(fma(b * b, A[0], fma(2.0 * a * b, A[1], a * a * A[2])), Bm[0]);
+        qe[2] = make_double2(fma(b, Bm[0], a * Bm[1]), 0.0);
+    }
 }
 
 __global__ void __launch_bounds__(128)
@@ -413,46 +440,22 @@ tree_chain_kernel(const TreeParams prm, int g)
 // leaves (the block of tree_block_kernel) and leaf t the inclusive prefix Q[t] of those five
 // moments over the block's leaves up to t is kept in the BLOCK's centred coordinate; the core's
 // whole leaves inside one block are then Q[t1 - 1] - Q[t0 - 1]: two 48-byte loads instead of a walk.
-// Leaves the shard's windows cannot reach count as empty (their nodes are not built).
-// Called by the first warp of the block's CTA after the leaves are built.
+// build_leaf leaves every leaf's own five moments (block coordinate; zeros for leaves the shard's
+// windows cannot reach) in its entry; the first warp of the block's CTA then scans them in place.
 __device__ __forceinline__ void build_core_prefix(const TreeParams& prm, int series, int32_t blk0,
                                                   int32_t blk1, int cb)
 {
     constexpr unsigned kFull = 0xffffffffu;
     const int lane = threadIdx.x & 31;
-    const double* __restrict__ x = prm.x + (size_t)series * (size_t)prm.n;
-    const double* base = prm.nodes + (size_t)series * prm.total * kNodeLen;
-    int32_t e0, e1, k0, k1;
-    node_span(0, blk0, prm.n, e0, k0);
-    node_span(0, blk1 - 1, prm.n, k1, e1);
-    const double xf = x[e0], xl = x[e1];
-    const double cB = 0.5 * xf + 0.5 * xl, dB = 0.5 * (xl - xf);
-    const double invB = dB > 0.0 ? 1.0 / dB : 0.0;
     const int per = (1 << cb) >> 5;                               // leaves per lane (cb >= 5)
     const int32_t first = blk0 + lane * per;
-    auto leaf_in_block = [&](int32_t leaf, double* m) -> bool {   // leaf moments in block coordinates
-        if (leaf >= blk1) return false;
-        int32_t j0, j1;
-        node_span(0, leaf, prm.n, j0, j1);
-        if (!node_needed(prm, series, j0, j1)) return false;
-        const double* nd = base + (size_t)leaf * kNodeLen;        // written by this CTA: plain loads
-        const double a = nd[1] * invB, b = (nd[0] - cB) * invB;
-        const double A0 = nd[2], A1 = nd[3], A2 = nd[4], B0 = nd[2 + kKA], B1 = nd[3 + kKA];
-        m[0] = A0;
-        m[1] = fma(b, A0, a * A1);
-        m[2] = fma(b * b, A0, fma(2.0 * a * b, A1, a * a * A2));
-        m[3] = B0;
-        m[4] = fma(b, B0, a * B1);
-        return true;
-    };
-    double tot[5] = {0.0, 0.0, 0.0, 0.0, 0.0}, m[5];
-    for (int r = 0; r < per; ++r)
-        if (leaf_in_block(first + r, m)) {
+    double* q = prm.qsum + ((size_t)series * prm.cnt[0] + first) * kQLen;   // written by build_leaf: plain loads
+    double tot[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+    for (int r = 0; r < per && first + r < blk1; ++r) {
 #pragma unroll
-            for (int k = 0; k < 5; ++k) tot[k] += m[k];
-        }
-    // exclusive scan of the lane totals
-    double run[5];
+        for (int k = 0; k < 5; ++k) tot[k] += q[(size_t)r * kQLen + k];
+    }
+    double run[5];                                                // exclusive scan of the lane totals
 #pragma unroll
     for (int k = 0; k < 5; ++k) {
         double v = tot[k];
@@ -463,19 +466,17 @@ __device__ __forceinline__ void build_core_prefix(const TreeParams& prm, int ser
         }
         run[k] = v - tot[k];
     }
-    double* q = prm.qsum + ((size_t)series * prm.cnt[0] + first) * kQLen;
-    for (int r = 0; r < per; ++r) {
-        if (first + r >= blk1) break;
-        if (leaf_in_block(first + r, m)) {
-#pragma unroll
-            for (int k = 0; k < 5; ++k) run[k] += m[k];
-        }
+    for (int r = 0; r < per && first + r < blk1; ++r) {
         double2* o = reinterpret_cast<double2*>(q + (size_t)r * kQLen);
+        const double2 e0 = o[0], e1 = o[1], e2 = o[2];
+        run[0] += e0.x; run[1] += e0.y; run[2] += e1.x; run[3] += e1.y; run[4] += e2.x;
         o[0] = make_double2(run[0], run[1]);
         o[1] = make_double2(run[2], run[3]);
         o[2] = make_double2(run[4], 0.0);
     }
     if (lane == 0) {
+        double cB, dB;
+        core_block_coord(prm, prm.x + (size_t)series * (size_t)prm.n, blk0 >> cb, cB, dB);
         double2* hd = reinterpret_cast<double2*>(prm.qhdr + ((size_t)series * ((prm.cnt[0] >> cb) + 1) + (blk0 >> cb)) * 2);
         *hd = make_double2(cB, dB);
     }
@@ -972,30 +973,32 @@ tree_eval_kernel(const TreeParams prm)
                 const double tt = fma(-(q * q), fabs(q), 1.0);
                 double wgt = (tt * tt) * tt;
                 wgt = ja >= l1 ? 1.0 : wgt;
-                wgt = k < ca ? wgt : 0.0;
                 const double wr = rw ? wgt * rw[ja] : wgt;
                 const double wq = wr * q;
                 const double yj = y[ja];
-                m.S0 += wr;
-                m.S1 += wq;
-                m.S2 = fma(wq, q, m.S2);
-                m.T0 = fma(wr, yj, m.T0);
-                m.T1 = fma(wq, yj, m.T1);
+                if (k < ca) {                 // predicated accumulation: no select on the weight
+                    m.S0 += wr;
+                    m.S1 += wq;
+                    m.S2 = fma(wq, q, m.S2);
+                    m.T0 = fma(wr, yj, m.T0);
+                    m.T1 = fma(wq, yj, m.T1);
+                }
             }
             {
                 const double q = (x[jb] - xs) * invh;
                 const double tt = fma(-(q * q), fabs(q), 1.0);
                 double wgt = (tt * tt) * tt;
                 wgt = jb <= r1 ? 1.0 : wgt;
-                wgt = k < cb ? wgt : 0.0;
                 const double wr = rw ? wgt * rw[jb] : wgt;
                 const double wq = wr * q;
                 const double yj = y[jb];
-                mb.S0 += wr;
-                mb.S1 += wq;
-                mb.S2 = fma(wq, q, mb.S2);
-                mb.T0 = fma(wr, yj, mb.T0);
-                mb.T1 = fma(wq, yj, mb.T1);
+                if (k < cb) {
+                    mb.S0 += wr;
+                    mb.S1 += wq;
+                    mb.S2 = fma(wq, q, mb.S2);
+                    mb.T0 = fma(wr, yj, mb.T0);
+                    mb.T1 = fma(wq, yj, mb.T1);
+                }
             }
         }
         m.S0 += mb.S0; m.S1 += mb.S1; m.S2 += mb.S2; m.T0 += mb.T0; m.T1 += mb.T1;
