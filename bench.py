@@ -59,8 +59,8 @@ TILE = 512                # output points per tile of the direct kernel
 # dram__bytes_read.sum + dram__bytes_write.sum of one fit_kernel launch, from the committed
 # `ncu --set full` captures (profiles/README.md); None where no capture exists.
 NCU_TRAFFIC = {
-    "c2": {"bytes": 48.5e6 + 349.2e6, "from": "profiles/r01_fit_kernel_c2_ncu_full.csv (mean of 2 launches; the K=10 "
-                                              "window split writes 350 MB of partial moments; 0.15% of DRAM peak)"},
+    "c2": {"bytes": 42.7e6 + 347.9e6, "from": "profiles/r02_fit_kernel_c2_ncu_full.csv (one launch of this code; the K=10 "
+                                              "window split writes 348 MB of partial moments; 0.15% of DRAM peak)"},
 }
 
 
@@ -253,8 +253,12 @@ class Env:
         self.rank = int(os.environ.get("RANK", "0"))
         self.local = int(os.environ.get("LOCAL_RANK", "0"))
         torch.cuda.set_device(self.local)
+        self.host_group = None
         if self.world > 1:
             dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+            # host-only rendezvous: an NCCL barrier is a kernel that SPINS on every waiting rank's GPU,
+            # which must stay idle while rank 0 alone drives all devices (one-process C-ABI arm)
+            self.host_group = dist.new_group(backend="gloo")
         self.lib = _lib.load()
         self.flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
         self.args = args
@@ -263,6 +267,11 @@ class Env:
         if self.world > 1:
             self.dist.barrier()
         self.torch.cuda.synchronize()
+
+    def host_barrier(self):
+        if self.world > 1:
+            self.torch.cuda.synchronize()
+            self.dist.barrier(group=self.host_group)
 
     def max_over_ranks(self, vals):
         if self.world == 1:
@@ -422,7 +431,8 @@ def measure_series(env, name, method, steps, warmup, want_e2e, clocks=None, samp
             a.close()
         del xp, yp, outs, shared
         # the same series through the C ABI from ONE process: cf_lowess_smooth_multi on rank 0
-        # drives all `world` devices (one host thread each) while the other ranks wait
+        # drives all `world` devices (one host thread each) while the other ranks wait ON THE HOST
+        env.host_barrier()
         if rank == 0:
             xp, yp = env.pinned(x), env.pinned(y)
             outs = tuple(env.pinned_empty(n) for _ in range(3))
@@ -452,7 +462,7 @@ def measure_series(env, name, method, steps, warmup, want_e2e, clocks=None, samp
                 regression.set_default_method("direct")
                 lib.cf_lowess_multi_release()
             del xp, yp, outs
-        env.barrier()
+        env.host_barrier()
     else:
         out["e2e"] = None
 

@@ -15,6 +15,7 @@
 // device list (a caller looping over smooth() pays for them once); cf_lowess_multi_release()
 // frees them.
 #include <algorithm>
+#include <chrono>
 #include <condition_variable>
 #include <mutex>
 #include <string>
@@ -161,7 +162,17 @@ int32_t cf_lowess_smooth_multi(const double* x_sorted, const double* y, int32_t 
         // only the elements the windows of [begin, end) can reach (shard_span_host, api.cu)
         int32_t lo = 0, hi = 0;
         shard_span_host(x_sorted, n, ns, h->begin, h->end, &lo, &hi);
+#ifdef CF_DEVELOPMENT
+        const auto t0 = std::chrono::steady_clock::now();
+        auto since = [&]() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); };
+#endif
         if (rc == CF_OK) rc = upload_span(h, x_sorted, y, lo, hi);
+#ifdef CF_DEVELOPMENT
+        const double t_enq = since();
+        cudaStreamSynchronize(h->stream);
+        cudaStreamSynchronize(h->copy_stream);
+        const double t_up = since();
+#endif
         if (rc != CF_OK) {
             fail(rc);
             std::lock_guard<std::mutex> g(bar.mu);
@@ -181,6 +192,11 @@ int32_t cf_lowess_smooth_multi(const double* x_sorted, const double* y, int32_t 
             if (e != cudaSuccess) rc = cuda_fail(e, "cf_lowess_smooth_multi download", __FILE__, __LINE__);
         }
         if (rc != CF_OK) fail(rc);
+#ifdef CF_DEVELOPMENT
+        if (dev_env("CF_MULTI_TIMES"))
+            fprintf(stderr, "[multi] rank %d dev %d: upload enqueued %.2f ms, landed %.2f ms ([%d, %d] = %.0f MB), all done %.2f ms\n",
+                    r, h->device, t_enq, t_up, lo, hi, 16e-6 * (hi - lo + 1), since());
+#endif
     };
     std::vector<std::thread> th;
     for (int r = 1; r < N; ++r) th.emplace_back(work, r);

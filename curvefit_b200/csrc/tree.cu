@@ -248,7 +248,8 @@ tree_merge_kernel(const TreeParams prm, int level)
     build_parent(prm, x, base, level, k, blockIdx.y);
 }
 
-// all levels from `level0` up in one CTA per series (they hold <= 2048 nodes)
+// all levels from `level0` up in one CTA per series (the first of them holds <= 256 nodes: one per
+// thread; with wider levels in here the CTA's serial trips cost 125 us per pass at n = 1e8)
 __global__ void __launch_bounds__(256)
 tree_top_kernel(const TreeParams prm, int level0)
 {
@@ -1136,7 +1137,7 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
             CF_CUDA(cudaGetLastError());
             h->launches++;
         }
-        for (; level < L && prm.cnt[level] > 2048; ++level) {
+        for (; level < L && prm.cnt[level] > 256; ++level) {     // one launch per level while it fills more than a CTA
             tree_merge_kernel<<<dim3((prm.cnt[level] + 127) / 128, h->nseries), 128, 0, h->stream>>>(prm, level);
             CF_CUDA(cudaGetLastError());
             h->launches++;
