@@ -153,6 +153,17 @@ static int residuals_and_robust_update(cf_lowess* h)
     return launch_bisquare(h);
 }
 
+// upload_span leaves y's copy in flight on the copy stream: whatever touches y next on the
+// handle's stream waits for it first
+static int wait_pending_y(cf_lowess* h)
+{
+    if (h->y_pending) {
+        CF_CUDA(cudaStreamWaitEvent(h->stream, h->ev_copy[1], 0));
+        h->y_pending = false;
+    }
+    return CF_OK;
+}
+
 static int begin_stage(cf_lowess* h, double f)
 {
     if (!h->init) { set_error("No data has been defined."); return CF_NO_DATA_DEFINED_ERROR; }
@@ -169,11 +180,7 @@ static int begin_stage(cf_lowess* h, double f)
         h->win_f = f;
     }
     h->ns = ns;
-    if (h->y_pending) {                    // upload_span: y arrives on the copy stream
-        CF_CUDA(cudaStreamWaitEvent(h->stream, h->ev_copy[1], 0));
-        h->y_pending = false;
-    }
-    return CF_OK;
+    return wait_pending_y(h);              // upload_span: y arrives on the copy stream
 }
 
 // evaluator of handles created from now on and of the stateless calls (cf_set_default_method)
@@ -282,6 +289,7 @@ static int32_t init_common(cf_lowess* h, const void* x, const void* y, int32_t n
     if (!h) { set_error("null handle"); return CF_INVALID_INPUT_ERROR; }
     if (n < 0 || (n > 0 && (!x || !y))) { set_error("Input array sizes must match."); return CF_ARRAY_SIZE_ERROR; }
     CF_TRY(use_device(h));
+    CF_TRY(wait_pending_y(h));                         // an earlier span upload must not land after this one
     h->init = false;                                   // :758
     h->win_f = -1.0;
     h->delta_built = -1.0;
@@ -486,6 +494,7 @@ int32_t cf_lowess_init_batched(cf_lowess* h, const double* x, const double* y, i
         return CF_ARRAY_SIZE_ERROR;
     }
     CF_TRY(use_device(h));
+    CF_TRY(wait_pending_y(h));
     h->init = false;
     h->win_f = -1.0;
     h->rank = 0; h->nranks = 1;
@@ -822,6 +831,7 @@ int32_t cf_lowess_fetch_xy(cf_lowess* h, double* xs, double* ysrt)
 {
     if (!h || !h->init) { set_error("No data has been defined."); return CF_NO_DATA_DEFINED_ERROR; }
     CF_TRY(use_device(h));
+    CF_TRY(wait_pending_y(h));
     const size_t bytes = sizeof(double) * (size_t)h->n * (size_t)h->nseries;
     if (xs) CF_CUDA(cudaMemcpyAsync(xs, h->x, bytes, cudaMemcpyDeviceToHost, h->stream));
     if (ysrt) CF_CUDA(cudaMemcpyAsync(ysrt, h->y, bytes, cudaMemcpyDeviceToHost, h->stream));
