@@ -520,6 +520,7 @@ int32_t cf_lowess_set_shard(cf_lowess* h, int32_t rank, int32_t nranks)
     CF_TRY(use_device(h));
     if (rank != h->rank || nranks != h->nranks) {
         h->win_f = -1.0;           // windows cover the shard only
+        h->delta_built = -1.0;     // and so do the slots of the fitted-point list
         peer_detach(h);            // the peers' block layout changes
     }
     h->rank = rank;
@@ -567,8 +568,8 @@ int32_t cf_lowess_set_delta(cf_lowess* h, double delta)
         set_error("delta must be finite and >= 0");
         return CF_INVALID_INPUT_ERROR;
     }
-    if (delta > 0.0 && (h->nseries != 1 || h->nranks != 1)) {
-        set_error("delta > 0 is supported for a single series on one GPU");
+    if (delta > 0.0 && h->nseries != 1) {
+        set_error("delta > 0 is supported for a single series (not for batched handles)");
         return CF_INVALID_INPUT_ERROR;
     }
     if (delta != h->delta) h->win_f = -1.0;

@@ -208,6 +208,8 @@ struct cf_lowess {
     double delta = 0.0;
     double delta_built = -1.0;           // delta the lists below were built for
     int32_t nfit = 0;
+    int32_t slot_begin = 0, slot_end = 0; // slots of fidx this shard fits: its own fitted points and the one
+                                          // fitted point before / after its block (the interpolation needs both)
     int32_t* fidx = nullptr;             // fitted points, ascending
     int32_t* fcend = nullptr;            // end of the tie chain of each fitted point (`last`, :681-689)
     int32_t* frank = nullptr;            // n + 1: number of fitted points < p

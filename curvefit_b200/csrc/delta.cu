@@ -101,11 +101,11 @@ delta_list_kernel(const int32_t* __restrict__ D, const int32_t* __restrict__ cen
 // Points that were not fitted (:674-680, :685-688), then res = y - ys (:695).
 __global__ void __launch_bounds__(256)
 delta_fill_kernel(const double* __restrict__ x, const double* __restrict__ y, double* __restrict__ ys,
-                  double* __restrict__ res, int32_t n, const int32_t* __restrict__ D,
+                  double* __restrict__ res, int32_t begin, int32_t end, const int32_t* __restrict__ D,
                   const int32_t* __restrict__ fidx, const int32_t* __restrict__ fcend)
 {
-    const int32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= n) return;
+    const int32_t j = begin + blockIdx.x * blockDim.x + threadIdx.x;     // the shard's points
+    if (j >= end) return;
     const int32_t k = D[j + 1] - 1;          // the last fitted point at or before j
     const int32_t a = fidx[k];
     double v = ys[a];
@@ -135,8 +135,8 @@ void delta_free(cf_lowess* h)
 int delta_prepare(cf_lowess* h)
 {
     if (!(h->delta > 0.0) || h->delta_built == h->delta) return CF_OK;
-    if (h->nseries != 1 || h->nranks != 1) {
-        set_error("delta > 0 is supported for a single series on one GPU");
+    if (h->nseries != 1) {
+        set_error("delta > 0 is supported for a single series (not for batched handles)");
         return CF_INVALID_INPUT_ERROR;
     }
     const int32_t n = h->n;
@@ -188,15 +188,37 @@ int delta_prepare(cf_lowess* h)
         if (e != cudaSuccess) fail(e, "delta list");
         else { h->nfit = m; h->delta_built = h->delta; }
     }
+    if (rc == CF_OK) {
+        // Range-sharded series: every rank derives the whole list (it holds all of x) and fits the
+        // slots of its own block [begin, end) plus the last fitted point at or before `begin` and
+        // the first one past the block -- delta_fill_kernel interpolates between them (:675-679) --
+        // so no fitted value has to cross ranks.  D(p) = number of fitted points below p.
+        h->slot_begin = 0;
+        h->slot_end = h->nfit;
+        if (h->nranks > 1 && h->end > h->begin) {
+            int32_t d[2] = {0, 0};
+            cudaError_t e = cudaMemcpyAsync(&d[0], h->frank + h->begin + 1, sizeof(int32_t), cudaMemcpyDeviceToHost, s);
+            if (e == cudaSuccess) e = cudaMemcpyAsync(&d[1], h->frank + h->end, sizeof(int32_t), cudaMemcpyDeviceToHost, s);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+            if (e != cudaSuccess) fail(e, "delta slots");
+            else {
+                h->slot_begin = d[0] > 0 ? d[0] - 1 : 0;
+                h->slot_end = d[1] + 1 < h->nfit ? d[1] + 1 : h->nfit;
+            }
+        } else if (h->nranks > 1) {
+            h->slot_end = 0;                               // empty shard
+        }
+    }
     cudaFree(tmp);
     return rc;
 }
 
 int launch_delta_fill(cf_lowess* h)
 {
-    const int32_t n = h->n;
-    delta_fill_kernel<<<(n + 255) / 256, 256, 0, h->stream>>>(h->x, h->y, h->ys, h->res, n, h->frank,
-                                                              h->fidx, h->fcend);
+    const int32_t cnt = h->end - h->begin;
+    if (cnt <= 0) return CF_OK;
+    delta_fill_kernel<<<(cnt + 255) / 256, 256, 0, h->stream>>>(h->x, h->y, h->ys, h->res, h->begin, h->end,
+                                                                h->frank, h->fidx, h->fcend);
     CF_CUDA(cudaGetLastError());
     h->launches++;
     return CF_OK;

@@ -586,7 +586,7 @@ int launch_fit(cf_lowess* h, bool use_rw)
     prm.x = h->x; prm.y = h->y; prm.rw = use_rw ? h->rw : nullptr; prm.ys = h->ys;
     prm.w = h->win; prm.n = h->n; prm.ns = h->ns; prm.begin = h->begin; prm.end = h->end;
     prm.ksplit = 1; prm.part = nullptr; prm.fidx = nullptr;
-    if (h->delta > 0.0) { prm.fidx = h->fidx; prm.begin = 0; prm.end = h->nfit; }
+    if (h->delta > 0.0) { prm.fidx = h->fidx; prm.begin = h->slot_begin; prm.end = h->slot_end; }
     if (h->sms <= 0) {
         int sms = 0;
         CF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));

@@ -1024,7 +1024,7 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
     prm.x = h->x; prm.y = h->y; prm.rw = use_rw ? h->rw : nullptr; prm.ys = h->ys;
     prm.w = h->win; prm.n = h->n; prm.ns = h->ns; prm.begin = h->begin; prm.end = h->end;
     prm.fidx = nullptr;
-    if (h->delta > 0.0) { prm.fidx = h->fidx; prm.begin = 0; prm.end = h->nfit; }
+    if (h->delta > 0.0) { prm.fidx = h->fidx; prm.begin = h->slot_begin; prm.end = h->slot_end; }
     int L = 0;
     int64_t total = 0;
     int32_t cnt = (h->n + kLeaf - 1) / kLeaf;

@@ -179,7 +179,7 @@ int launch_windows(cf_lowess* h, int32_t ns)
     if (h->n < 2) return CF_OK;
     const int threads = 256;
     const bool listed = h->delta > 0.0;
-    const int32_t begin = listed ? 0 : h->begin, end = listed ? h->nfit : h->end;
+    const int32_t begin = listed ? h->slot_begin : h->begin, end = listed ? h->slot_end : h->end;
     const int cnt = end - begin;
     span_init_kernel<<<(h->nseries + 255) / 256, 256, 0, h->stream>>>(h->span, h->nseries);
     if (cnt <= 0) return CF_OK;

@@ -224,7 +224,10 @@ CF_API int32_t cf_set_default_method(int32_t method);
 CF_API int32_t cf_default_method(void);
 
 /* delta of later runs on this handle (default 0 = every distinct x is fitted).
- * delta > 0: single series, one GPU (no batched / sharded handles). */
+ * delta > 0: single series (no batched handles).  On a range-sharded handle every rank
+ * derives the whole fitted-point list (it must hold all of x: cf_lowess_init, not
+ * cf_lowess_init_span) and fits the points of its block plus the fitted point before and
+ * after it, so the interpolation needs no exchange. */
 CF_API int32_t cf_lowess_set_delta(cf_lowess* h, double delta);
 CF_API double cf_lowess_delta(const cf_lowess* h);
 /* After a run with delta > 0: number of points lowest() was called on and their

@@ -23,10 +23,12 @@ def main():
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     ok = True
-    cases = [(50_000, 0.1, 3, "random"), (200_000, 0.05, 2, "grid"), (3000, 0.3, 2, "ties"),
-             (300_000, 0.2, 3, "random")]
+    # (n, f, nsteps, x family, delta as a fraction of the x range; 0 = every point fitted)
+    cases = [(50_000, 0.1, 3, "random", 0.0), (200_000, 0.05, 2, "grid", 0.0), (3000, 0.3, 2, "ties", 0.0),
+             (300_000, 0.2, 3, "random", 0.0),
+             (200_000, 0.1, 2, "random", 0.002), (60_000, 0.3, 3, "ties", 0.01), (100_000, 0.05, 2, "grid", 0.0005)]
     for transport, method in [("nccl", "direct"), ("p2p", "direct"), ("p2p", "tree")]:
-      for n, f, nsteps, kind in cases:
+      for n, f, nsteps, kind, dfrac in cases:
           if kind == "grid":
               x = datagen.grid_x(n)
           elif kind == "ties":
@@ -38,12 +40,17 @@ def main():
           solo = lowess_smoothing(device=local)
           solo.set_method(method)
           solo.initialize(x, y, srt=False)
+          delta = dfrac * float(x[-1] - x[0])
+          if delta > 0:
+              solo.set_delta(delta)
           ys_ref = solo.smooth(f, nsteps=nsteps)
           rw_ref, res_ref = solo.m_weights.copy(), solo.m_residuals.copy()
 
           fit = lowess_smoothing(device=local, stream=stream)
           fit.set_method(method)
           fit.initialize(x, y, srt=False)
+          if delta > 0:
+              fit.set_delta(delta)      # every rank derives the whole fitted-point list, fits its block's slots
           stages = DeviceStages(fit, rank, world)
           if transport == "p2p":
               assert stages.attach_peers(), "peer attach failed"
@@ -61,7 +68,7 @@ def main():
           perr = stages.peer_error() if transport == "p2p" else False
           good = d_ys <= 1e-12 and d_rw <= 1e-9 and d_res <= 1e-12 and d_c <= 1e-12 and not perr
           ok &= bool(good)
-          print(f"[rank {rank}/{world}] {transport}/{method} n={n} f={f} nsteps={nsteps} {kind}: |dys|={d_ys:.2e} |drw|={d_rw:.2e} "
+          print(f"[rank {rank}/{world}] {transport}/{method} n={n} f={f} nsteps={nsteps} {kind} delta={delta:.3g}: |dys|={d_ys:.2e} |drw|={d_rw:.2e} "
                 f"|dres|={d_res:.2e} dcmad={d_c:.2e} bitwise_ys={np.array_equal(ys, ys_ref)} "
                 f"collectives={job.collectives} {'OK' if good else 'FAIL'}", flush=True)
           stages.detach_peers()     # collective; before any rank frees its buffers
