@@ -108,8 +108,8 @@ def test_smooth_multi_ties_and_device_lists(oracle):
 
 @needs2
 def test_one_process_per_gpu_paths_match_single_gpu():
-    """torchrun, 2 ranks: NCCL transport + direct, peer-memory transport + direct / tree,
-    four series each, every rank compares with its own single-GPU run."""
+    """torchrun, 2 ranks: NCCL transport + direct, peer-memory transport + direct / tree, seven
+    series each (three of them with delta > 0), every rank compares with its own single-GPU run."""
     env = dict(os.environ)
     env.pop("OMP_NUM_THREADS", None)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
