@@ -278,6 +278,8 @@ void cf_lowess_destroy(cf_lowess* h)
     delta_free(h);
     for (auto& ev : h->ev) if (ev) cudaEventDestroy(ev);
     for (auto& ev : h->ev_copy) if (ev) cudaEventDestroy(ev);
+    for (cudaEvent_t ev : h->chunk_events) cudaEventDestroy(ev);
+    cudaFree(h->build_span_buf);
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -678,15 +680,17 @@ static int32_t run_passes(cf_lowess* h, int32_t passes, bool first_uses_rw, cf_s
     NvtxRange whole("cf_lowess passes");
     for (int32_t p = 0; p < passes && rc == CF_OK; ++p) {          // :657
         if ((rc = mark()) != CF_OK) break;
-        const bool chunked = p + 1 == passes && h->early_ys && h->copy_stream && method_is_tree(h) &&
+        const bool skip_fit = p == 0 && h->first_fit_done;         // issued chunk by chunk during the upload
+        const bool chunked = p + 1 == passes && !skip_fit && h->early_ys && h->copy_stream && method_is_tree(h) &&
                              h->nseries == 1 && !(h->delta > 0.0) && h->end - h->begin >= (1 << 22);
         if (chunked) {
             NvtxRange r("lowest pass (last, in pieces beside the download)");
             if ((rc = last_pass_chunked(h, use_rw)) != CF_OK) break;
+            h->last_in_pieces = true;
             if ((rc = mark()) != CF_OK) break;
             break;
         }
-        {
+        if (!skip_fit) {
             NvtxRange r(use_rw ? "lowest pass (robustness weights)" : "lowest pass (first)");
             if ((rc = launch_fit(h, use_rw)) != CF_OK) break;      // :662-693
         }
@@ -732,6 +736,7 @@ static int32_t run_passes(cf_lowess* h, int32_t passes, bool first_uses_rw, cf_s
     h->timing = false;
     h->early_rw = nullptr;                 // one-shot
     h->early_ys = h->early_res = nullptr;
+    h->first_fit_done = false;
     for (cudaEvent_t e : h->marks) cudaEventDestroy(e);
     h->marks.clear();
     for (cudaEvent_t e : evs) cudaEventDestroy(e);
@@ -1028,6 +1033,105 @@ int32_t cf_sort_xy(const double* x, const double* y, int32_t n, double* x_sorted
     return rc;
 }
 
+__global__ void __launch_bounds__(256)
+fill_kernel(double* __restrict__ x, int64_t n, double v)
+{
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += stride) x[k] = v;
+}
+
+__global__ void set_build_span_kernel(int32_t* sp, int32_t lo, int32_t hi, int32_t top_hi)
+{
+    sp[0] = lo; sp[1] = hi; sp[2] = 0; sp[3] = top_hi;
+}
+
+// cf_lowess_smooth on a long series, tree evaluator: the series is uploaded in chunks and the FIRST
+// pass (windows, tree build, evaluation) follows the upload chunk by chunk instead of waiting for
+// all of it (at n = 1e8 the upload is 32 ms, the first pass 25 ms).
+//  * x starts as +inf everywhere except x(n) (lowest() needs x(n) - x(1), :535), so every guided
+//    search of windows.cu that probes past the arrived elements meets a monotone predicate;
+//  * a point is processed once x(i + ns) has arrived (windows.cu reads x(L + ns), L <= i; its
+//    window ends at or before i + ns - 1) and the run of values equal to its window's last one
+//    has ended;
+//  * chunks are multiples of every power-of-two node span the chunk-gated build kernels handle
+//    (binary levels with more than 256 nodes: < n / 256 elements; chain blocks: <= ns / 2), so
+//    no such node straddles a chunk; the few top levels are rebuilt over everything that has arrived.
+// Node values, windows and fitted values are those of the undivided pass, bit for bit.
+static int first_pass_pipelined(cf_lowess* h, const double* x, const double* y, double f)
+{
+    const int32_t n = h->n;
+    const int32_t ns = cf_lowess_span(n, f);
+    int64_t align = 1;
+    while (align < (int64_t)n / 256 || align < (int64_t)ns / 2) align <<= 1;
+    if (align < 16 * 512) align = 16 * 512;
+    int64_t chunk = ((int64_t)n / 12 + align - 1) / align * align;
+    if (chunk < align) chunk = align;
+    const int C = (int)(((int64_t)n + chunk - 1) / chunk);
+    while ((int)h->chunk_events.size() < C) {
+        cudaEvent_t e;
+        CF_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        h->chunk_events.push_back(e);
+    }
+    if (!h->build_span_buf) CF_CUDA(cudaMalloc(&h->build_span_buf, 4 * sizeof(int32_t)));
+    int32_t* const span_dev = h->build_span_buf;
+    h->ns = ns;
+    CF_TRY(select_prepare(h));
+    fill_kernel<<<296, 256, 0, h->stream>>>(h->x, (int64_t)n - 1, (double)INFINITY);
+    CF_CUDA(cudaGetLastError());
+    CF_CUDA(cudaMemcpyAsync(h->x + (n - 1), x + (n - 1), sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    CF_CUDA(cudaEventRecord(h->ev_copy[0], h->stream));
+    CF_CUDA(cudaStreamWaitEvent(h->copy_stream, h->ev_copy[0], 0));
+    h->launches++;
+    int rc = CF_OK;
+    int32_t p0 = 0;
+    bool first_windows = true;
+    for (int k = 0; k < C && rc == CF_OK; ++k) {
+        const int64_t e0 = (int64_t)k * chunk, e1 = e0 + chunk < n ? e0 + chunk : n;
+        const size_t bytes = sizeof(double) * (size_t)(e1 - e0);
+        cudaError_t e = cudaMemcpyAsync(h->x + e0, x + e0, bytes, cudaMemcpyHostToDevice, h->copy_stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(h->y + e0, y + e0, bytes, cudaMemcpyHostToDevice, h->copy_stream);
+        if (e == cudaSuccess) e = cudaEventRecord(h->chunk_events[(size_t)k], h->copy_stream);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(h->stream, h->chunk_events[(size_t)k], 0);
+        if (e != cudaSuccess) { rc = cuda_fail(e, "pipelined upload", __FILE__, __LINE__); break; }
+        // points whose windows lie inside what has arrived: i + ns < e1, and -- a window of equal
+        // abscissas (h = 0) takes every element equal to xs, however far the run goes (:546) -- the
+        // window's last value must be below the last arrived one, whose run may continue in the next chunk
+        int64_t p1 = n;
+        if (k < C - 1) {
+            const int64_t tfirst = std::lower_bound(x, x + e1, x[e1 - 1]) - x;    // first element of that run
+            p1 = tfirst - ns + 1;
+        }
+        if (p1 < p0) p1 = p0;
+        if (p1 > p0) {
+            rc = launch_windows_range(h, ns, p0, (int32_t)p1, first_windows);
+            first_windows = false;
+            if (rc != CF_OK) break;
+        }
+        // the tree over the new elements (+ the top levels over everything so far)
+        set_build_span_kernel<<<1, 1, 0, h->stream>>>(span_dev, (int32_t)e0, (int32_t)(e1 - 1), (int32_t)(e1 - 1));
+        h->build_span = span_dev;
+        h->tree_build_only = true;
+        h->begin = 0; h->end = n;
+        rc = launch_fit(h, false);
+        h->tree_build_only = false;
+        h->build_span = nullptr;
+        if (rc != CF_OK) break;
+        if (p1 > p0) {
+            h->begin = p0; h->end = (int32_t)p1;
+            h->tree_skip_build = true;
+            rc = launch_fit(h, false);                 // :662-693 for these points, first pass (userw = .false.)
+            h->tree_skip_build = false;
+            p0 = (int32_t)p1;
+        }
+    }
+    h->begin = 0; h->end = n;
+    if (rc == CF_OK) {
+        h->win_f = f;
+        h->first_fit_done = true;
+    }
+    return rc;
+}
+
 int32_t cf_lowess_smooth(const double* x_sorted, const double* y, int32_t n, double f,
                          int32_t nsteps, double* ys, double* rw, double* res)
 {
@@ -1055,26 +1159,32 @@ int32_t cf_lowess_smooth(const double* x_sorted, const double* y, int32_t n, dou
         CF_TRY(layout_series(h, n));                                  // ls_init, srt = .false. (:800-803)
         CF_TRY(ensure_copy_stream(h));
         const size_t bytes = sizeof(double) * (size_t)n;
-        CF_CUDA(cudaMemcpyAsync(h->x, x_sorted, bytes, cudaMemcpyHostToDevice, h->stream));
-        CF_CUDA(cudaEventRecord(h->ev_copy[0], h->stream));
-        // y follows x over the bus on the second stream while the window search (x only) runs
-        CF_CUDA(cudaStreamWaitEvent(h->copy_stream, h->ev_copy[0], 0));
-        CF_CUDA(cudaMemcpyAsync(h->y, y, bytes, cudaMemcpyHostToDevice, h->copy_stream));
-        CF_CUDA(cudaEventRecord(h->ev_copy[1], h->copy_stream));
-        h->win_f = -1.0;
-        CF_TRY(begin_stage(h, f));                                    // windows
-        CF_CUDA(cudaStreamWaitEvent(h->stream, h->ev_copy[1], 0));
-        h->early_rw = (rw && nsteps > 0) ? rw : nullptr;
-        // tree evaluator: ys and res leave piece by piece during the last pass (run_passes)
+        // tree evaluator: the first pass follows the upload chunk by chunk, and ys / res leave piece
+        // by piece during the last pass (run_passes)
         h->ns = cf_lowess_span(n, f);
         const bool pieces = method_is_tree(h) && n >= (1 << 22);
+        if (pieces) {
+            CF_TRY(first_pass_pipelined(h, x_sorted, y, f));
+        } else {
+            CF_CUDA(cudaMemcpyAsync(h->x, x_sorted, bytes, cudaMemcpyHostToDevice, h->stream));
+            CF_CUDA(cudaEventRecord(h->ev_copy[0], h->stream));
+            // y follows x over the bus on the second stream while the window search (x only) runs
+            CF_CUDA(cudaStreamWaitEvent(h->copy_stream, h->ev_copy[0], 0));
+            CF_CUDA(cudaMemcpyAsync(h->y, y, bytes, cudaMemcpyHostToDevice, h->copy_stream));
+            CF_CUDA(cudaEventRecord(h->ev_copy[1], h->copy_stream));
+            h->win_f = -1.0;
+            CF_TRY(begin_stage(h, f));                                // windows
+            CF_CUDA(cudaStreamWaitEvent(h->stream, h->ev_copy[1], 0));
+        }
+        h->early_rw = (rw && nsteps > 0) ? rw : nullptr;
         h->early_ys = pieces ? ys : nullptr;
         h->early_res = pieces ? res : nullptr;
+        h->last_in_pieces = false;
         int rc2 = cf_lowess_run(h, f, nsteps, nullptr);
         h->early_rw = nullptr;
         h->early_ys = h->early_res = nullptr;
         if (rc2 != CF_OK) { cudaStreamSynchronize(h->copy_stream); return rc2; }
-        if (!pieces) {
+        if (!h->last_in_pieces) {
             CF_CUDA(cudaMemcpyAsync(ys, h->ys, bytes, cudaMemcpyDeviceToHost, h->stream));
             if (res) CF_CUDA(cudaMemcpyAsync(res, h->res, bytes, cudaMemcpyDeviceToHost, h->stream));
         }

@@ -232,6 +232,15 @@ struct cf_lowess {
     double* early_ys = nullptr;           // cf_lowess_smooth: host destinations of ys / res, downloaded chunk by
     double* early_res = nullptr;          //   chunk while the last pass of the tree evaluator is still running
     bool tree_skip_build = false;         // tree.cu: evaluate only (the pass's tree is built)
+    bool tree_build_only = false;         // tree.cu: build only
+    // pipelined first pass of cf_lowess_smooth (api.cu): the tree is built chunk by chunk as the
+    // elements arrive; build_span[0..1] gates the block / merge / chain kernels to the new chunk,
+    // build_span[2..3] the top levels to everything that has arrived (device ints; null: h->span)
+    int32_t* build_span = nullptr;        // active only while a chunk is being built
+    int32_t* build_span_buf = nullptr;    // its allocation
+    std::vector<cudaEvent_t> chunk_events;
+    bool first_fit_done = false;          // run_passes: the first fit pass was already issued
+    bool last_in_pieces = false;          // run_passes evaluated the last pass in pieces and sent ys / res home
     bool y_pending = false;               // y's upload is in flight on copy_stream (ev_copy[1])
 
     // counters for cf_stats
@@ -244,6 +253,7 @@ namespace cf {
 
 // kernels' host launchers (each returns CF_OK or an error code; async on h->stream)
 int launch_windows(cf_lowess* h, int32_t ns);
+int launch_windows_range(cf_lowess* h, int32_t ns, int32_t begin, int32_t end, bool init_span);   // a sub-range of points
 int launch_fit(cf_lowess* h, bool use_rw);        // dispatches on h->method
 int launch_fit_tree(cf_lowess* h, bool use_rw);   // tree.cu
 bool method_is_tree(const cf_lowess* h);

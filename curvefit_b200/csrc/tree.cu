@@ -1105,7 +1105,9 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
     prm.nodes = h->tree;
     prm.qsum = h->tree + node_doubles;
     prm.qhdr = prm.qsum + qsum_doubles;
-    prm.span = h->span;
+    prm.span = h->build_span ? h->build_span : h->span;       // what the build is gated to
+    TreeParams ptop = prm;                                     // the top levels: everything that has arrived
+    if (h->build_span) ptop.span = h->build_span + 2;
     auto mark = [&]() {
         if (!h->timing) return;
         cudaEvent_t e;
@@ -1143,7 +1145,7 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
             h->launches++;
         }
         if (level < L) {
-            tree_top_kernel<<<h->nseries, 256, 0, h->stream>>>(prm, level);
+            tree_top_kernel<<<h->nseries, 256, 0, h->stream>>>(ptop, level);
             CF_CUDA(cudaGetLastError());
             h->launches++;
         }
@@ -1160,6 +1162,7 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
         }
     }
     mark();
+    if (h->tree_build_only) return CF_OK;
     const int cntp = prm.end - prm.begin;
     // 7 CTAs of 128 threads per SM (72 registers), tricube nodes staged per warp, core nodes read
     // directly; the others are kept for measurement in development builds (B200, n = 1e8 smooth,

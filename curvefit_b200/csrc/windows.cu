@@ -174,14 +174,13 @@ __global__ void span_init_kernel(int32_t* span, int32_t nseries)
     if (s < nseries) { span[2 * s] = INT32_MAX; span[2 * s + 1] = -1; }
 }
 
-int launch_windows(cf_lowess* h, int32_t ns)
+int launch_windows_range(cf_lowess* h, int32_t ns, int32_t begin, int32_t end, bool init_span)
 {
     if (h->n < 2) return CF_OK;
     const int threads = 256;
     const bool listed = h->delta > 0.0;
-    const int32_t begin = listed ? h->slot_begin : h->begin, end = listed ? h->slot_end : h->end;
     const int cnt = end - begin;
-    span_init_kernel<<<(h->nseries + 255) / 256, 256, 0, h->stream>>>(h->span, h->nseries);
+    if (init_span) span_init_kernel<<<(h->nseries + 255) / 256, 256, 0, h->stream>>>(h->span, h->nseries);
     if (cnt <= 0) return CF_OK;
     // points per thread: as many as leave about two waves of threads on the device
     const int64_t total = (int64_t)cnt * h->nseries;
@@ -194,6 +193,12 @@ int launch_windows(cf_lowess* h, int32_t ns)
     CF_CUDA(cudaGetLastError());
     h->launches++;
     return CF_OK;
+}
+
+int launch_windows(cf_lowess* h, int32_t ns)
+{
+    const bool listed = h->delta > 0.0;
+    return launch_windows_range(h, ns, listed ? h->slot_begin : h->begin, listed ? h->slot_end : h->end, true);
 }
 
 }  // namespace cf
