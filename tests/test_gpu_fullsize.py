@@ -219,7 +219,7 @@ def test_windows_guided_searches_large_irregular(cf, kind):
     assert np.all((r1 == i) | inside(r1, h1)) and np.all((r1 == r9) | ~inside(r1 + 1, h1))
 
 
-@pytest.mark.parametrize("kind", ["grid", "ties"])
+@pytest.mark.parametrize("kind", ["grid", "ties", "run"])
 def test_host_buffer_smooth_with_overlapped_copies_equals_resident_run(cf, kind):
     """cf_lowess_smooth on a long series overlaps its copies with the kernels: direct evaluator --
     y's upload beside the window search, the final weights' download beside the last pass; tree
@@ -227,9 +227,18 @@ def test_host_buffer_smooth_with_overlapped_copies_equals_resident_run(cf, kind)
     ys / res leave piece by piece during the last pass, which is evaluated in pieces.  Every output
     must equal the plain sequence init -> run -> fetch bit for bit."""
     n, f, nsteps = 6_000_000, 0.002, 2
-    x = datagen.grid_x(n) if kind == "grid" else np.sort(np.round(datagen.random_x(n, 9) * (n // 6)) / (n // 6))
+    if kind == "grid":
+        x = datagen.grid_x(n)
+    elif kind == "ties":
+        x = np.sort(np.round(datagen.random_x(n, 9) * (n // 6)) / (n // 6))
+    else:
+        # a run of 1.5e6 equal abscissas across three upload chunks: windows inside it have h = 0 and
+        # take the whole run (:546) -- its points may only be processed once the run has ended
+        u = datagen.random_x(n - 1_500_000, 9)
+        x = np.sort(np.concatenate([0.4 * u[: u.size // 2], np.full(1_500_000, 0.5), 0.6 + 0.4 * u[u.size // 2:]]))
     y = datagen.noisy_y(x, 9)
-    for method, nsteps in (("tree", 2), ("direct", 2), ("tree", 0)):
+    plan = (("tree", 2), ("tree", 0)) if kind == "run" else (("tree", 2), ("direct", 2), ("tree", 0))
+    for method, nsteps in plan:
         fit = cf.lowess_smoothing()
         fit.set_method(method)
         fit.initialize(x, y, srt=False)
