@@ -25,7 +25,7 @@
 // numerically benign).  Each range is cut segment-tree fashion into
 // O(log ns) nodes plus < 16 elements at either end that are evaluated
 // directly with the reference's formula.  Because rw changes every
-// robustness iteration, the tree is rebuilt per pass (O(n); 5 of the 27 ms of
+// robustness iteration, the tree is rebuilt per pass (O(n); 5.4 of the 22.5 ms of
 // a pass at n = 1e8), one launch per block of leaves (tree_block_kernel).
 //
 // Chains.  A range's two boundary paths would cost one node per binary level.  On top of
@@ -36,7 +36,9 @@
 // covers it).  A boundary path then climbs cbits[g] binary levels per node (suffix on the
 // left path, prefix on the right path); only the top, where both ends fall into one block,
 // uses binary nodes.  The launcher picks the geometry from ns (one level of 16 bits at ns = 5e6):
-// n = 1e8, ns = 5e6: about 12 tricube nodes per point instead of 36.
+// n = 1e8, ns = 5e6: 6.5 tricube-node steps per warp instead of ~36 nodes per point on the plain
+// binary tree.  The w = 1 core does not walk at all: its whole leaves come from per-block prefix sums
+// of the five low-order moments (build_core_prefix).
 //
 // This backend is separate from fit.cu (the direct kernel that carries the
 // FP64 roofline claim); cf_lowess_set_method() selects it.
