@@ -59,6 +59,7 @@ SIGNATURES = {
     "cf_lowess_init": (C.c_int32, [C.c_void_p, c_dp, c_dp, C.c_int32, C.c_int32]),
     "cf_lowess_init_device": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32]),
     "cf_lowess_shard_span": (C.c_int32, [C.c_void_p, c_dp, C.c_int32, C.c_double, c_ip, c_ip]),
+    "cf_lowess_block_span": (C.c_int32, [c_dp, C.c_int32, C.c_double, C.c_int32, C.c_int32, c_ip, c_ip]),
     "cf_lowess_init_span": (C.c_int32, [C.c_void_p, c_dp, c_dp, C.c_int32, C.c_int32, C.c_int32]),
     "cf_lowess_fetch_block": (C.c_int32, [C.c_void_p, c_dp, c_dp, c_dp]),
     "cf_lowess_set_early_weights": (C.c_int32, [C.c_void_p, c_dp]),

@@ -411,17 +411,36 @@ int upload_span(cf_lowess* h, const double* x, const double* y, int32_t lo, int3
     return CF_OK;
 }
 
-// The elements the windows of output points [begin, end) can reach, computed on the host from
-// the sorted abscissas: windows.cu reads x(L + ns) for L <= i, so [begin - ns, end - 1 + ns],
-// widened over ties -- a window with h = 0 takes every point equal to xs (:546), and the leader
-// of a tie group may lie below.  A superset of [min lo9, max hi9].
+// nleft of point i (0-based) as windows.cu finds it: the first L in [0, n - ns] with
+// x(i) - x(L) <= x(L + ns) - x(i)  (src/curvefit_regression.f90:664-666; monotone in L)
+static int64_t host_nleft(const double* x, int64_t n, int64_t ns, int64_t i)
+{
+    const double xs = x[i];
+    int64_t lo = 0, hi = n - ns;                       // the predicate holds at n - ns by construction
+    while (lo < hi) {
+        const int64_t mid = lo + ((hi - lo) >> 1);
+        const double d1 = xs - x[mid], d2 = x[mid + ns] - xs;
+        if (d1 <= d2) hi = mid; else lo = mid + 1;
+    }
+    return lo;
+}
+
+// The elements the windows of output points [begin, end) reach, computed on the host from the
+// sorted abscissas: nleft is monotone in i, so they start at nleft(begin) and end at
+// nright(end - 1) = nleft(end - 1) + ns - 1, plus the one element beyond that the searches of
+// windows.cu test (x(L + ns), the first excluded point), widened over ties -- a window with h = 0
+// takes every point equal to xs (:546).  On a grid that is block + ns / 2 either side: the
+// (ns-1)-point halo is the worst case (blocks at the ends of the series).
 void shard_span_host(const double* x, int32_t n, int32_t ns, int32_t begin, int32_t end, int32_t* lo_out,
                      int32_t* hi_out)
 {
-    int64_t lo = (int64_t)begin - ns, hi = (int64_t)end - 1 + ns;
-    if (lo < 0) lo = 0;
+    if (end > n) end = n;
+    if (begin >= end) begin = end > 0 ? end - 1 : 0;
+    int64_t lo = host_nleft(x, n, ns, begin);
+    int64_t hi = host_nleft(x, n, ns, end > 0 ? end - 1 : 0) + ns;       // nright + 1
     if (hi > n - 1) hi = n - 1;
-    if (hi < lo) hi = lo;
+    if (lo > begin) lo = begin;
+    if (hi < end - 1) hi = end - 1;
     lo = std::lower_bound(x, x + lo, x[lo]) - x;
     hi = (std::upper_bound(x + hi, x + n, x[hi]) - x) - 1;
     *lo_out = (int32_t)lo;
@@ -443,6 +462,20 @@ int32_t cf_lowess_shard_span(const cf_lowess* h, const double* x_sorted, int32_t
     const int32_t begin = (int32_t)(b < n ? b : n), end = (int32_t)(b + per < n ? b + per : n);
     int32_t lo = 0, hi = 0;
     shard_span_host(x_sorted, n, cf_lowess_span(n, f), begin < n ? begin : n - 1, end, &lo, &hi);
+    *first = lo + 1;
+    *last = hi + 1;
+    return CF_OK;
+}
+
+int32_t cf_lowess_block_span(const double* x_sorted, int32_t n, double f, int32_t begin, int32_t end,
+                             int32_t* first, int32_t* last)
+{
+    if (!x_sorted || n < 1 || !first || !last || begin < 1 || end < begin || end > n || !(f == f)) {
+        set_error("cf_lowess_block_span: bad argument");
+        return CF_INVALID_INPUT_ERROR;
+    }
+    int32_t lo = 0, hi = 0;
+    shard_span_host(x_sorted, n, cf_lowess_span(n, f), begin - 1, end, &lo, &hi);
     *first = lo + 1;
     *last = hi + 1;
     return CF_OK;

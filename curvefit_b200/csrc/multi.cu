@@ -5,8 +5,8 @@
 // The sorted index range is cut into `ndev` equal blocks of output points (same
 // partition and the same kernels as the one-process-per-GPU path of distributed.py).  One
 // host thread per device:
-//   * uploads only the elements its block's windows can reach -- [begin - ns, end - 1 + ns]
-//     widened over ties: the (ns-1)-point halo -- not the whole series;
+//   * uploads only the elements its block's windows can reach -- nleft(begin) .. nright(end - 1) + 1
+//     widened over ties: at most the (ns-1)-point halo either side -- not the whole series;
 //   * runs the passes (cf_lowess_run on a peer-attached handle: the histogram all-reduce of the
 //     median, the candidate exchange and the halo weights cross NVLink inside the kernels,
 //     peer.cu; the peers are mapped with cudaDeviceEnablePeerAccess, no IPC);

@@ -176,10 +176,15 @@ CF_API int32_t cf_lowess_init_device(cf_lowess* h, const void* d_x, const void* 
  * first .. last (1-based, inclusive) are uploaded; x outside becomes -inf / +inf sentinels
  * (x(1) and x(n) keep their values: lowest() needs x(n) - x(1), :535), y outside is
  * untouched.  cf_lowess_shard_span gives the span the handle's shard (cf_lowess_set_shard)
- * needs for span fraction f: the shard's block plus ns elements on either side, widened over
- * ties -- the (ns-1)-point halo.  cf_lowess_fetch_block copies only the shard's own block
+ * needs for span fraction f: from nleft of the block's first point to nright + 1 of its last one,
+ * widened over ties -- at most the (ns-1)-point halo either side, ns / 2 on a grid.  cf_lowess_fetch_block copies only the shard's own block
  * [begin, end) of ys, rw, res into full-length host arrays (each may be NULL). */
 CF_API int32_t cf_lowess_shard_span(const cf_lowess* h, const double* x_sorted, int32_t n, double f,
+                                    int32_t* first, int32_t* last);
+/* The same for an arbitrary block of output points begin .. end (1-based, inclusive); needs no
+ * handle and no device: nleft(begin) .. nright(end) + 1 by the reference's own predicate
+ * (:664-666), widened over ties. */
+CF_API int32_t cf_lowess_block_span(const double* x_sorted, int32_t n, double f, int32_t begin, int32_t end,
                                     int32_t* first, int32_t* last);
 CF_API int32_t cf_lowess_init_span(cf_lowess* h, const double* x_sorted, const double* y, int32_t n,
                                    int32_t first, int32_t last);

@@ -199,3 +199,39 @@ def test_cmake_build_produces_the_same_abi(tmp_path):
     assert not missing, missing
     sass = subprocess.run(["cuobjdump", "-lelf", so], capture_output=True, text=True).stdout
     assert "sm_100a" in sass and "sm_90" not in sass
+
+
+@pytest.mark.parametrize("kind", ["grid", "uniform", "clustered", "ties", "equal", "wide"])
+@pytest.mark.parametrize("n,f", [(3000, 0.1), (5000, 0.6), (777, 0.02)])
+def test_block_span_covers_every_window_of_the_block(kind, n, f):
+    """cf_lowess_block_span (host-only: what a rank of a range-sharded series uploads) against the
+    oracle's recorded windows: for every block of output points the span must contain each point's
+    nleft .. nrt (the sweep stops ON the first excluded point, :553-554), its tie-group leader and
+    the extra element the window search tests, and it must not exceed the (ns-1)-point halo."""
+    from oracle import oracle
+    from tests import cases
+    oracle.build()
+    lib = _lib.load()
+    x = cases.make_x(kind, n, 11)
+    y = cases.make_y(x, 11)
+    ns = max(min(int(f * float(n)), n), 2)
+    r = oracle.lowess(x, y, f, 0, want_windows=True)
+    lead = np.searchsorted(x, x, side="left")                       # 0-based leader of every point
+    nl = r["nleft"][lead] - 1                                        # followers take their leader's window
+    nrt = r["nrt"][lead] - 1
+    nr = r["nright"][lead] - 1
+    p = lambda a: a.ctypes.data_as(_lib.c_dp)
+    for parts in (1, 2, 3, 7):
+        edges = np.linspace(0, n, parts + 1).astype(int)
+        for b, e in zip(edges[:-1], edges[1:]):
+            if e <= b:
+                continue
+            first, last = C.c_int32(), C.c_int32()
+            rc = lib.cf_lowess_block_span(p(x), n, f, int(b) + 1, int(e), C.byref(first), C.byref(last))
+            assert rc == 0
+            lo, hi = first.value - 1, last.value - 1
+            assert lo <= min(nl[b:e].min(), lead[b:e].min()), (kind, b, e)
+            assert hi >= min(max(nrt[b:e].max(), nr[b:e].max() + 1), n - 1), (kind, b, e)
+            if kind not in ("ties", "equal"):                        # ties widen it legitimately
+                assert lo >= b - ns and hi <= e - 1 + ns, (kind, b, e)
+    assert lib.cf_lowess_block_span(p(x), n, f, 0, 5, C.byref(first), C.byref(last)) == 201
