@@ -366,6 +366,28 @@ def cf_lowess_smooth(x_sorted, y, f, nsteps=2, out=None):
     return ys, rw, res
 
 
+def cf_lowess_smooth_multi(x_sorted, y, f, nsteps=2, devices=None, out=None):
+    """cf_lowess_smooth over several GPUs of the box from this one process (csrc/multi.cu):
+    the series is range-sharded over `devices` (None = every visible device), each device
+    receives only its block + halo and writes its own block of the result."""
+    lib = _lib.load()
+    x = np.ascontiguousarray(x_sorted, dtype=np.float64)
+    y = np.ascontiguousarray(y, dtype=np.float64)
+    n = x.size
+    if out is None:
+        out = (np.empty(n), np.zeros(n), np.zeros(n))
+    ys, rw, res = out
+    if devices is None:
+        devs, ndev = None, 0
+    else:
+        devs = (C.c_int32 * len(devices))(*[int(d) for d in devices])
+        ndev = len(devices)
+    rc = lib.cf_lowess_smooth_multi(_dp(x), _dp(y), n, float(f), int(nsteps), devs, ndev, _dp(ys), _dp(rw), _dp(res))
+    if rc != 0:
+        raise RuntimeError(f"cf_lowess_smooth_multi failed ({rc}): {_lib.last_error()}")
+    return ys, rw, res
+
+
 def cf_lowess_smooth_delta(x_sorted, y, f, nsteps=2, delta=0.0):
     """lowess(x, y, f, nsteps, delta, ys, rw, res) (:625-715) through the host-buffer C ABI."""
     lib = _lib.load()
