@@ -29,7 +29,7 @@ static int fail(const char* what, int32_t rc)
 int main(void)
 {
     enum { N = 100 };
-    double x[N], y[N], xs[N], ys_in[N], ys[N], rw[N], res[N];
+    double x[N], y[N], xs[N], ys_in[N], ys[N], rw[N], res[N], ys2[N], rw2[N], res2[N];
     uint32_t lcg = 12345u;
     int32_t rc, i;
 
@@ -54,5 +54,16 @@ int main(void)
         printf("x = %.4f  y = % .4f  ys = % .4f  rw = %.4f  res = % .4f\n", xs[i], ys_in[i], ys[i], rw[i], res[i]);
     for (i = 0; i < N; ++i)
         if (!(res[i] == ys_in[i] - ys[i])) { fprintf(stderr, "res != y - ys at %d\n", (int)i); return 1; }
+
+    /* what the shim's smooth() calls for long series: every visible GPU from this one process
+     * (devices = NULL); a series this short runs on one device and must give the same answer */
+    rc = cf_lowess_smooth_multi(xs, ys_in, N, 0.2, 2, NULL, 0, ys2, rw2, res2);
+    if (rc != CF_OK) return fail("cf_lowess_smooth_multi", rc);
+    for (i = 0; i < N; ++i)
+        if (ys2[i] != ys[i] || rw2[i] != rw[i] || res2[i] != res[i]) {
+            fprintf(stderr, "cf_lowess_smooth_multi differs at %d\n", (int)i);
+            return 1;
+        }
+    cf_lowess_multi_release();
     return 0;
 }
