@@ -405,23 +405,39 @@ def measure_series(env, name, method, steps, warmup, want_e2e, clocks=None, samp
     elif want_e2e:
         from curvefit_b200.distributed import SharedHostArray
         xp, yp = env.pinned(x), env.pinned(y)
-        shared = [SharedHostArray(n) for _ in range(3)]      # ys, rw, res: one host result all ranks map
-        outs = tuple(a.array for a in shared)
-        job.smooth_host(xp, yp, f, nsteps, outs, shared_out=True)
+        # one host result all ranks map (POSIX shared memory); where /dev/shm is too small for it the
+        # older form is timed instead: every rank uploads the series, rank 0 reads everything back
+        room = [False]
+        if rank == 0:
+            try:
+                fs = os.statvfs("/dev/shm")
+                room[0] = fs.f_bavail * fs.f_frsize > 3 * 8 * n + (64 << 20)
+            except OSError:
+                room[0] = False
+        env.dist.broadcast_object_list(room, src=0, group=env.host_group)
+        shared_out = bool(room[0])
+        shared = [SharedHostArray(n) for _ in range(3)] if shared_out else []      # ys, rw, res
+        if shared_out:
+            outs = tuple(a.array for a in shared)
+        else:
+            outs = tuple(env.pinned_empty(n) for _ in range(3)) if rank == 0 else None
+        job.smooth_host(xp, yp, f, nsteps, outs, shared_out=shared_out)
         reps = max(1, min(steps, 3))
         env.barrier()
         t0 = time.perf_counter()
         for _ in range(reps):
-            job.smooth_host(xp, yp, f, nsteps, outs, shared_out=True)
+            job.smooth_host(xp, yp, f, nsteps, outs, shared_out=shared_out)
         env.barrier()
         dt = env.max_over_ranks([(time.perf_counter() - t0) / reps])[0]
         up = torch.tensor([float(job.last_upload)], device="cuda", dtype=torch.float64)
         env.dist.all_reduce(up)
         out["e2e"] = {"value": n / dt, "unit": "points/s", "h2d_bytes_per_step": int(16 * up.item()),
                       "d2h_bytes_per_step": 24 * n, "ms_per_step": dt * 1e3,
-                      "api": "ShardedLowess.smooth_host(host x, y -> host ys, rw, res in shared page-locked memory): "
-                             "each rank uploads its block + (ns-1)-point halo and writes its own block of the "
-                             "result; wall clock incl. the closing barrier, max over ranks"}
+                      "api": ("ShardedLowess.smooth_host(host x, y -> host ys, rw, res in shared page-locked memory): "
+                              "each rank uploads its block + halo and writes its own block of the "
+                              "result; wall clock incl. the closing barrier, max over ranks") if shared_out else
+                             ("ShardedLowess.smooth_host(host x, y on every rank -> host ys, rw, res on rank 0; "
+                              "/dev/shm too small for the shared result), pinned buffers, wall clock, max over ranks")}
         if rank == 0 and ys_solo is not None:                   # the assembled host result vs one GPU
             d = float(np.max(np.abs(outs[0] - ys_solo)))
             out["e2e"]["max_abs_diff_ys_vs_single_gpu"] = d
