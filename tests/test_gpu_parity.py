@@ -317,3 +317,25 @@ def test_robust_step_on_degenerate_residuals(cf, oracle, kind):
     ys0, _, res0 = fit.run_from_rw(f, None, passes=1)
     cmad, rw_ref = oracle.robust_weights(res0)
     assert np.array_equal(rw1, rw_ref), kind
+
+
+def test_fewer_than_two_points_return_y_and_touch_nothing_else(cf):
+    """lowess with n < 2 (:651-654): ys = y and the routine returns before rw or res are
+    written; n = 0 is a no-op.  Through the stateless call, the multi-GPU call (one device
+    here) and the type."""
+    from curvefit_b200 import _lib
+    lib = _lib.load()
+    p = lambda a: a.ctypes.data_as(_lib.c_dp)
+    for fn, extra in ((lib.cf_lowess_smooth, ()), (lib.cf_lowess_smooth_multi, (None, 0))):
+        x, y = np.array([0.25]), np.array([3.5])
+        ys, rw, res = np.full(1, -7.0), np.full(1, -8.0), np.full(1, -9.0)
+        assert fn(p(x), p(y), 1, 0.5, 2, *extra, p(ys), p(rw), p(res)) == 0
+        assert ys[0] == 3.5 and rw[0] == -8.0 and res[0] == -9.0
+        e = np.zeros(0)
+        assert fn(p(e), p(e), 0, 0.5, 2, *extra, p(e), p(e), p(e)) == 0
+        assert fn(p(x), p(y), -1, 0.5, 2, *extra, p(ys), p(rw), p(res)) == 202      # CF_ARRAY_SIZE_ERROR
+        assert fn(p(x), p(y), 1, 0.5, -1, *extra, p(ys), p(rw), p(res)) == 201     # CF_INVALID_INPUT_ERROR
+    fit = cf.lowess_smoothing()
+    fit.initialize(np.array([0.25]), np.array([3.5]))
+    assert fit.get_count() == 1
+    assert np.array_equal(fit.smooth(0.3), np.array([3.5]))
