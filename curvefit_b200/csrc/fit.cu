@@ -157,8 +157,10 @@ __device__ __forceinline__ void tile_setup(const FitParams& prm, int32_t tile0, 
             hmax = fmax(hmax, h);
             if (h > 0.0) hmin = fmin(hmin, h);
         } else {
+            // an idle slot (tie follower, past the tile's end) constrains nothing: its sums are
+            // never stored, so the warp's predicate-free chunks may run over it with any weights
+            // (it used to switch them off for the whole warp -- every warp of a series with ties)
             t.hp[p] = 0.0; t.xsp[p] = 0.0;
-            flo = INT32_MAX; fhi = -1;                // no fast chunks for this warp
         }
         rng[0][loc] = l9; rng[1][loc] = r9; rng[2][loc] = l1; rng[3][loc] = r1;
     }
