@@ -53,6 +53,7 @@ SIGNATURES = {
     "cf_moving_average_device": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
     "cf_median": (C.c_int32, [c_dp, C.c_int32, c_dp]),
     "cf_median_device": (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),
+    "cf_median_device_noalloc": (C.c_int32, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),
     "cf_sort": (C.c_int32, [c_dp, C.c_int32, c_dp]),
     "cf_lowess_create": (C.c_int32, [C.POINTER(C.c_void_p), C.c_int32, C.c_void_p]),
     "cf_lowess_destroy": (None, [C.c_void_p]),

@@ -16,6 +16,8 @@
 // cost per update = one FP64 subtract, divide, add.
 #include "common.cuh"
 
+#include <mutex>
+
 namespace cf {
 
 template <int NT, int C>
@@ -171,3 +173,61 @@ int32_t cf_median_device(const void* d_x, int32_t n, void* d_z, void* stream)
 }
 
 }  // extern "C"
+
+// ---- cf_median_device_noalloc ---------------------------------------------------------------
+// The select's scratch (state | two histograms | candidate list, select_scratch_bytes(n)) lives in
+// the library image instead of coming from cudaMallocAsync: one fixed array per GPU that loads
+// this library, sized for CF_MEDIAN_NOALLOC_MAX_N elements (about 8.2 MB), held until the process
+// exits.  See the declaration in curvefit_cuda.h for who needs this and what it costs.
+namespace {
+
+constexpr size_t kNoAllocScratchBytes =
+    256 + (sizeof(unsigned int) << cf::kSelB0Single) + 2 * (sizeof(unsigned int) << cf::kSelWSingle)
+    + sizeof(unsigned long long) * (size_t)CF_MEDIAN_NOALLOC_MAX_N;
+
+// `g_median_scratch` is a device symbol.  Device code may name it; in HOST code the name is only a
+// stand-in the runtime uses to look the symbol up -- it is not a device address and must never be
+// handed to a kernel or to cudaMemsetAsync.  median_noalloc_scratch() asks the runtime for the real
+// address on the CURRENT device (each device has its own copy of the array).
+static __device__ __align__(256) unsigned char g_median_scratch[kNoAllocScratchBytes];
+
+constexpr int kNoAllocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+void* g_noalloc_ptr[kNoAllocMaxDevices];        // device address of g_median_scratch, per device ordinal
+
+int median_noalloc_scratch(void** out)
+{
+    int dev = -1;
+    CF_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kNoAllocMaxDevices) {
+        cf::set_error("cf_median_device_noalloc: device ordinal beyond the per-device table (64)");
+        return CF_DEVICE_ERROR;
+    }
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev]) {                  // first call on this device: resolve the symbol once
+        void* p = nullptr;
+        CF_CUDA(cudaGetSymbolAddress(&p, g_median_scratch));
+        if (!p) { cf::set_error("cf_median_device_noalloc: scratch symbol has no device address"); return CF_DEVICE_ERROR; }
+        g_noalloc_ptr[dev] = p;
+    }
+    *out = g_noalloc_ptr[dev];
+    return CF_OK;
+}
+
+}  // namespace
+
+extern "C" int32_t cf_median_device_noalloc(const void* d_x, int32_t n, void* d_z, void* stream)
+{
+    if (n < 1 || !d_x || !d_z) { set_error("Input array sizes must match."); return CF_ARRAY_SIZE_ERROR; }
+    if (n > CF_MEDIAN_NOALLOC_MAX_N || select_scratch_bytes(n) > kNoAllocScratchBytes) {
+        set_error("cf_median_device_noalloc: n = %d exceeds the built-in scratch (at most %d elements); "
+                  "use cf_median_device", (int)n, (int)CF_MEDIAN_NOALLOC_MAX_N);
+        return CF_ARRAY_SIZE_ERROR;
+    }
+    void* scratch = nullptr;
+    CF_TRY(median_noalloc_scratch(&scratch));
+    // select_median zeroes the state and both histograms itself (cudaMemsetAsync on `stream`), so
+    // what the previous call left in the array does not matter; the candidate list is write-before-read.
+    return select_median(static_cast<const double*>(d_x), n, static_cast<double*>(d_z), scratch,
+                         (cudaStream_t)stream, nullptr);
+}

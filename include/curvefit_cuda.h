@@ -133,6 +133,31 @@ CF_API int32_t cf_median(const double* x, int32_t n, double* z);
  * default stream, as for cf_moving_average_device); scratch is allocated in stream order. */
 CF_API int32_t cf_median_device(const void* d_x, int32_t n, void* d_z, void* stream);
 
+/* cf_median_device for callers that must not allocate device memory.  No counterpart in the
+ * reference (it has no device memory at all); it exists because cf_median_device takes its select
+ * scratch from cudaMallocAsync, and some callers cannot afford or are not allowed that:
+ *   - a process in which another allocator (a framework's caching pool, a fixed arena set up at
+ *     start-up) already owns all of the GPU's memory, so a driver allocation fails or evicts;
+ *   - devices or virtualised set-ups without stream-ordered memory pools, where cudaMallocAsync
+ *     is simply not available;
+ *   - latency-bound loops (control, acquisition) that have finished their set-up phase and may not
+ *     take the driver's allocation locks or an implicit synchronisation any more.
+ * Here the scratch is a fixed array inside the library image: about 8.2 MB of device memory on EVERY
+ * GPU that loads libcurvefit_cuda, held until the process exits whether or not this function is
+ * ever called.  Limit: n <= CF_MEDIAN_NOALLOC_MAX_N; larger n returns CF_ARRAY_SIZE_ERROR with a
+ * message and touches nothing.  Same result as cf_median_device, bit for bit.
+ *   - The caller still owns d_x (n doubles) and d_z (one double), both on the CURRENT device, and
+ *     `stream` (NULL = legacy default stream) must belong to the current device too.
+ *   - The first call on each device looks up the array's device address (one runtime query, no
+ *     allocation) and caches it; make that first call outside any stream capture.
+ *   - All calls on a device share the one array.  Each call clears the counters it needs itself, so
+ *     back-to-back calls on one stream are fine; two calls that can run on the GPU at the same time
+ *     (different streams without an ordering between them, or two host threads) race on it and
+ *     return garbage.  Serialise them, or use cf_median_device for the concurrent ones.
+ * Calls no cudaMalloc / cudaFree / cudaMallocAsync and no allocating library routine. */
+#define CF_MEDIAN_NOALLOC_MAX_N 1048576
+CF_API int32_t cf_median_device_noalloc(const void* d_x, int32_t n, void* d_z, void* stream);
+
 /* sort(x, .true.) (LINALG linalg_sorting.f90:12-35 -> DLASRT 'I'): ascending values
  * by the device radix sort.  In and out may not alias. */
 CF_API int32_t cf_sort(const double* x, int32_t n, double* x_sorted);
