@@ -49,6 +49,7 @@ SIGNATURES = {
     "cf_lowess_smooth_multi": (C.c_int32, [c_dp, c_dp, C.c_int32, C.c_double, C.c_int32, c_ip, C.c_int32,
                                            c_dp, c_dp, c_dp]),
     "cf_lowess_multi_release": (C.c_int32, []),
+    "cf_lowess_multi_active": (C.c_int32, []),
     "cf_moving_average": (C.c_int32, [c_dp, C.c_int32, C.c_int32]),
     "cf_moving_average_device": (C.c_int32, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
     "cf_median": (C.c_int32, [c_dp, C.c_int32, c_dp]),

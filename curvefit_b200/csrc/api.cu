@@ -295,6 +295,7 @@ static int32_t init_common(cf_lowess* h, const void* x, const void* y, int32_t n
     h->init = false;                                   // :758
     h->win_f = -1.0;
     h->delta_built = -1.0;
+    h->x_partial = false;
     h->nseries = 1;
     CF_TRY(reserve(h, n));
     h->n = n;
@@ -354,6 +355,7 @@ int layout_series(cf_lowess* h, int32_t n)
     h->init = false;
     h->win_f = -1.0;
     h->delta_built = -1.0;
+    h->x_partial = false;
     h->nseries = 1;
     CF_TRY(reserve(h, n));
     h->n = n;
@@ -390,6 +392,7 @@ int upload_span(cf_lowess* h, const double* x, const double* y, int32_t lo, int3
     CF_TRY(use_device(h));
     h->win_f = -1.0;                                   // new data: new neighbourhoods
     h->delta_built = -1.0;
+    h->x_partial = lo > 1 || hi < h->n - 2;            // sentinels are written below exactly then
     const size_t bytes = sizeof(double) * (size_t)(hi - lo + 1);
     CF_TRY(ensure_copy_stream(h));
     CF_CUDA(cudaMemcpyAsync(h->x + lo, x + lo, bytes, cudaMemcpyHostToDevice, h->stream));
@@ -504,6 +507,8 @@ int32_t cf_lowess_fetch_block(cf_lowess* h, double* ys, double* rw, double* res)
 {
     if (!h || !h->init || h->nseries != 1) { set_error("No data has been defined."); return CF_NO_DATA_DEFINED_ERROR; }
     CF_TRY(use_device(h));
+    if (!rw && h->early_rw_missed) rw = h->early_rw_missed;   // cf_lowess_set_early_weights, not issued by the run
+    h->early_rw_missed = nullptr;
     if (h->end > h->begin) {
         const size_t b = sizeof(double) * (size_t)(h->end - h->begin), o = (size_t)h->begin;
         if (ys) CF_CUDA(cudaMemcpyAsync(ys + o, h->ys + o, b, cudaMemcpyDeviceToHost, h->stream));
@@ -533,6 +538,7 @@ int32_t cf_lowess_init_batched(cf_lowess* h, const double* x, const double* y, i
     h->init = false;
     h->win_f = -1.0;
     h->rank = 0; h->nranks = 1;
+    h->x_partial = false;
     CF_TRY(reserve(h, n, nseries));
     h->n = n;
     h->nseries = nseries;
@@ -605,6 +611,11 @@ int32_t cf_lowess_set_delta(cf_lowess* h, double delta)
     }
     if (delta > 0.0 && h->nseries != 1) {
         set_error("delta > 0 is supported for a single series (not for batched handles)");
+        return CF_INVALID_INPUT_ERROR;
+    }
+    if (delta > 0.0 && h->x_partial) {
+        set_error("delta > 0 needs the whole of x on the handle (cf_lowess_init), not a span upload "
+                  "(cf_lowess_init_span): the fitted-point list is derived from every abscissa");
         return CF_INVALID_INPUT_ERROR;
     }
     if (delta != h->delta) h->win_f = -1.0;
@@ -709,6 +720,8 @@ static int32_t run_passes(cf_lowess* h, int32_t passes, bool first_uses_rw, cf_s
     };
     int rc = CF_OK;
     bool use_rw = first_uses_rw;
+    bool early_rw_issued = false;
+    h->early_rw_missed = nullptr;
     h->timing = timed;
     NvtxRange whole("cf_lowess passes");
     for (int32_t p = 0; p < passes && rc == CF_OK; ++p) {          // :657
@@ -734,11 +747,14 @@ static int32_t run_passes(cf_lowess* h, int32_t passes, bool first_uses_rw, cf_s
             use_rw = true;
             if (p + 2 == passes && h->early_rw && h->copy_stream) {
                 // m_weights are final: their download runs beside the last fit pass
-                cudaEventRecord(h->ev_copy[0], h->stream);
-                cudaStreamWaitEvent(h->copy_stream, h->ev_copy[0], 0);
-                cudaMemcpyAsync(h->early_rw + h->begin, h->rw + h->begin,
-                                sizeof(double) * (size_t)(h->end - h->begin), cudaMemcpyDeviceToHost,
-                                h->copy_stream);
+                cudaError_t e = cudaEventRecord(h->ev_copy[0], h->stream);
+                if (e == cudaSuccess) e = cudaStreamWaitEvent(h->copy_stream, h->ev_copy[0], 0);
+                if (e == cudaSuccess && h->end > h->begin)
+                    e = cudaMemcpyAsync(h->early_rw + h->begin, h->rw + h->begin,
+                                        sizeof(double) * (size_t)(h->end - h->begin), cudaMemcpyDeviceToHost,
+                                        h->copy_stream);
+                if (e != cudaSuccess) { rc = cuda_fail(e, "early download of the robustness weights", __FILE__, __LINE__); break; }
+                early_rw_issued = true;
             }
         } else {
             if ((rc = launch_residuals(h)) != CF_OK) break;        // :695
@@ -767,6 +783,9 @@ static int32_t run_passes(cf_lowess* h, int32_t passes, bool first_uses_rw, cf_s
         st->ms_tree_build = build;
     }
     h->timing = false;
+    // asked for and there are final weights (a robustness update ran), but the copy was not issued
+    // (no copy stream): the fetch that follows must not assume the weights have left
+    if (rc == CF_OK && passes >= 2 && h->early_rw && !early_rw_issued) h->early_rw_missed = h->early_rw;
     h->early_rw = nullptr;                 // one-shot
     h->early_ys = h->early_res = nullptr;
     h->first_fit_done = false;
@@ -790,6 +809,7 @@ int32_t cf_lowess_run(cf_lowess* h, double f, int32_t nsteps, cf_stats* st)
     if (h->n < 2) {                                                 // :651-654
         if (h->n == 1) CF_CUDA(cudaMemcpyAsync(h->ys, h->y, sizeof(double) * (size_t)h->nseries, cudaMemcpyDeviceToDevice, h->stream));
         CF_CUDA(cudaStreamSynchronize(h->stream));
+        h->early_rw = h->early_rw_missed = nullptr;                 // one-shot; there are no weights
     } else {
         CF_TRY(run_passes(h, nsteps + 1, false, st));
     }
@@ -1217,6 +1237,10 @@ int32_t cf_lowess_smooth(const double* x_sorted, const double* y, int32_t n, dou
         h->early_rw = nullptr;
         h->early_ys = h->early_res = nullptr;
         if (rc2 != CF_OK) { cudaStreamSynchronize(h->copy_stream); return rc2; }
+        if (h->early_rw_missed) {
+            CF_CUDA(cudaMemcpyAsync(rw, h->rw, bytes, cudaMemcpyDeviceToHost, h->stream));
+            h->early_rw_missed = nullptr;
+        }
         if (!h->last_in_pieces) {
             CF_CUDA(cudaMemcpyAsync(ys, h->ys, bytes, cudaMemcpyDeviceToHost, h->stream));
             if (res) CF_CUDA(cudaMemcpyAsync(res, h->res, bytes, cudaMemcpyDeviceToHost, h->stream));
@@ -1276,6 +1300,7 @@ int32_t cf_lowess_smooth_batched(const double* x_sorted, const double* y, int32_
         h->init = false;
         h->win_f = -1.0;
         h->rank = 0; h->nranks = 1;
+        h->x_partial = false;
         CF_TRY(reserve(h, n, cnt));
         h->n = n;
         h->nseries = cnt;

@@ -207,6 +207,8 @@ struct cf_lowess {
     // rest is tie-copied / interpolated (src/curvefit_regression.f90:674-690)
     double delta = 0.0;
     double delta_built = -1.0;           // delta the lists below were built for
+    bool x_partial = false;              // x holds -inf / +inf sentinels outside an uploaded span (upload_span):
+                                         // the fitted-point list of delta > 0 cannot be derived from it
     int32_t nfit = 0;
     int32_t slot_begin = 0, slot_end = 0; // slots of fidx this shard fits: its own fitted points and the one
                                           // fitted point before / after its block (the interpolation needs both)
@@ -229,6 +231,8 @@ struct cf_lowess {
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t ev_copy[2] = {};
     double* early_rw = nullptr;           // host destination of that download (null: none), full-length base
+    double* early_rw_missed = nullptr;    // a requested early download that the last run could NOT issue: whoever
+                                          // fetches the results copies the weights there instead
     double* early_ys = nullptr;           // cf_lowess_smooth: host destinations of ys / res, downloaded chunk by
     double* early_res = nullptr;          //   chunk while the last pass of the tree evaluator is still running
     bool tree_skip_build = false;         // tree.cu: evaluate only (the pass's tree is built)

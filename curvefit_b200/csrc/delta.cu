@@ -139,6 +139,13 @@ int delta_prepare(cf_lowess* h)
         set_error("delta > 0 is supported for a single series (not for batched handles)");
         return CF_INVALID_INPUT_ERROR;
     }
+    if (h->x_partial) {
+        // after a span upload x is -inf / +inf outside the span; the list built from that (:682-690)
+        // would differ from the reference's and from rank to rank
+        set_error("delta > 0 needs the whole of x on the handle (cf_lowess_init), not a span upload "
+                  "(cf_lowess_init_span)");
+        return CF_INVALID_INPUT_ERROR;
+    }
     const int32_t n = h->n;
     const size_t len = (size_t)n + 1;
     if ((int64_t)len > h->cap_delta) {

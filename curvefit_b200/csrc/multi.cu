@@ -35,6 +35,8 @@ struct MultiCtx {
 
 std::mutex g_multi_mu;            // one multi-GPU smooth at a time per process
 MultiCtx* g_multi = nullptr;
+std::vector<int> g_no_peer_devs;  // a device list whose peer mapping failed: peer access does not change
+                                  // while the process lives, so later calls go to one GPU at once
 
 void multi_free(MultiCtx* c)
 {
@@ -45,8 +47,10 @@ void multi_free(MultiCtx* c)
     delete c;
 }
 
-int multi_build(const std::vector<int>& devs, int32_t n, MultiCtx** out)
+// *no_peers: the per-device buffers fitted but the devices cannot map each other's memory
+int multi_build(const std::vector<int>& devs, int32_t n, MultiCtx** out, bool* no_peers)
 {
+    *no_peers = false;
     MultiCtx* c = new MultiCtx();
     c->devs = devs;
     c->n = n;
@@ -57,8 +61,15 @@ int multi_build(const std::vector<int>& devs, int32_t n, MultiCtx** out)
         if (rc == CF_OK) rc = cf_lowess_set_shard(c->hs[r], (int32_t)r, (int32_t)devs.size());
         if (rc == CF_OK) rc = layout_series(c->hs[r], n);
     }
-    if (rc == CF_OK) rc = cf_lowess_peer_attach_local(c->hs.data(), (int32_t)devs.size());
-    if (rc != CF_OK) { multi_free(c); return rc; }
+    if (rc == CF_OK) {
+        rc = cf_lowess_peer_attach_local(c->hs.data(), (int32_t)devs.size());
+        *no_peers = rc != CF_OK;
+    }
+    if (rc != CF_OK) {
+        multi_free(c);
+        for (int d : devs) { if (cudaSetDevice(d) == cudaSuccess) (void)cudaGetLastError(); }   // a failed cudaMalloc is not sticky
+        return rc;
+    }
     *out = c;
     return CF_OK;
 }
@@ -93,6 +104,12 @@ int32_t cf_lowess_multi_release(void)
     g_multi = nullptr;
     if (have) cudaSetDevice(dev);
     return CF_OK;
+}
+
+int32_t cf_lowess_multi_active(void)
+{
+    std::lock_guard<std::mutex> lk(g_multi_mu);
+    return g_multi ? (int32_t)g_multi->devs.size() : 0;
 }
 
 int32_t cf_lowess_smooth_multi(const double* x_sorted, const double* y, int32_t n, double f,
@@ -137,11 +154,30 @@ int32_t cf_lowess_smooth_multi(const double* x_sorted, const double* y, int32_t 
     }
     if (!(f == f)) { set_error("f is NaN"); return CF_INVALID_INPUT_ERROR; }
 
-    std::lock_guard<std::mutex> lk(g_multi_mu);
+    // The sharded run needs room for the buffers on every device and a peer mapping between all of
+    // them.  A box without P2P (PCIe without a switch, mixed GPUs, MIG slices) or a GPU another job
+    // has filled must not turn a smooth() that works on one GPU into an error: the context is
+    // freed and the whole series goes to ONE device -- the caller's if it is in the list, else the
+    // first of the list -- with identical results (cf_lowess_smooth).
+    auto one_gpu = [&]() -> int32_t {
+        const int d = std::count(devs.begin(), devs.end(), caller_dev) ? caller_dev : devs[0];
+        CF_CUDA(cudaSetDevice(d));
+        const int rc = cf_lowess_smooth(x_sorted, y, n, f, nsteps, ys, rw, res);
+        cudaSetDevice(caller_dev);
+        return rc;
+    };
+    std::unique_lock<std::mutex> lk(g_multi_mu);
     if (g_multi && (g_multi->n != n || g_multi->devs != devs)) { multi_free(g_multi); g_multi = nullptr; }
+    if (!g_multi && g_no_peer_devs == devs) { lk.unlock(); return one_gpu(); }
     if (!g_multi) {
-        const int rc = multi_build(devs, n, &g_multi);
-        if (rc != CF_OK) { cudaSetDevice(caller_dev); return rc; }
+        bool no_peers = false;
+        const int rc = multi_build(devs, n, &g_multi, &no_peers);
+        if (rc != CF_OK) {
+            g_multi = nullptr;
+            if (no_peers) g_no_peer_devs = devs;
+            lk.unlock();
+            return one_gpu();
+        }
     }
     MultiCtx* c = g_multi;
     const int N = (int)devs.size();
@@ -185,6 +221,9 @@ int32_t cf_lowess_smooth_multi(const double* x_sorted, const double* y, int32_t 
         if (rc == CF_OK) {
             const size_t cnt = (size_t)(h->end - h->begin), b = sizeof(double) * cnt;
             cudaError_t e = cudaMemcpyAsync(ys + h->begin, h->ys + h->begin, b, cudaMemcpyDeviceToHost, h->stream);
+            if (e == cudaSuccess && h->early_rw_missed)
+                e = cudaMemcpyAsync(rw + h->begin, h->rw + h->begin, b, cudaMemcpyDeviceToHost, h->stream);
+            h->early_rw_missed = nullptr;
             if (e == cudaSuccess && res)
                 e = cudaMemcpyAsync(res + h->begin, h->res + h->begin, b, cudaMemcpyDeviceToHost, h->stream);
             if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);

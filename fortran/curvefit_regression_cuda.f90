@@ -27,6 +27,8 @@ module curvefit_regression_cuda
     public :: moving_average
     ! additions that have no counterpart in the reference (nothing above changes meaning):
     public :: lowess_set_evaluator
+    public :: lowess_use_all_gpus
+    public :: lowess_release_gpus
     public :: CF_METHOD_DIRECT, CF_METHOD_TREE, CF_METHOD_AUTO
 
     !> Same generic name as the reference (src/curvefit_regression.f90:82-84).
@@ -42,9 +44,13 @@ module curvefit_regression_cuda
     integer(int32), parameter :: CF_METHOD_DIRECT = 0
     integer(int32), parameter :: CF_METHOD_TREE = 1
     integer(int32), parameter :: CF_METHOD_AUTO = 2
-    !> Series at least this long are smoothed on all GPUs of the box
-    !! (cf_lowess_smooth_multi); shorter ones on the current device.
+    !> Once lowess_use_all_gpus(.true.) has been called, series at least this long are
+    !! smoothed on all GPUs of the box (cf_lowess_smooth_multi); shorter ones, and every
+    !! series by default, on the current device.
     integer(int32), parameter :: CF_MULTI_GPU_MIN_POINTS = 4000000
+    !> Opt-in switch of the multi-GPU route (process-wide, default off): smooth() behaves
+    !! exactly as on a one-GPU box unless the program asks for more.
+    logical, save :: m_all_gpus = .false.
 
     type lowess_smoothing
         private
@@ -101,6 +107,14 @@ module curvefit_regression_cuda
             integer(c_int32_t) :: rc
         end function
 
+        ! frees the per-device buffers and the peer mapping cf_lowess_smooth_multi keeps
+        ! between calls (about 60 bytes per point on every GPU)
+        function cf_lowess_multi_release() bind(C, name = "cf_lowess_multi_release") &
+                result(rc)
+            import :: c_int32_t
+            integer(c_int32_t) :: rc
+        end function
+
         function cf_set_default_method(method) bind(C, name = "cf_set_default_method") &
                 result(rc)
             import :: c_int32_t
@@ -142,6 +156,27 @@ contains
         end if
         rc = cf_set_default_method(method)
         if (rc /= 0) call report(errmgr, "lowess_set_evaluator", rc)
+    end subroutine
+
+    !> Lets smooth() spread long series (CF_MULTI_GPU_MIN_POINTS or more) over every GPU of
+    !! the box.  Off by default: the sharded run keeps buffers for the whole series on every
+    !! device between calls, which a program sharing the box with other jobs may not want.
+    !! Where the GPUs cannot reach each other's memory, or one of them is full, the library
+    !! runs the call on one GPU instead of failing (include/curvefit_cuda.h).
+    subroutine lowess_use_all_gpus(flag)
+        logical, intent(in) :: flag
+        integer(int32) :: rc
+        m_all_gpus = flag
+        if (.not.flag) rc = cf_lowess_multi_release()
+    end subroutine
+
+    !> Frees what the multi-GPU route keeps on the devices between calls.  The type has no
+    !! finaliser (allocatable components only, like the reference, so that assignment still
+    !! deep-copies): a program that used lowess_use_all_gpus(.true.) calls this when it is
+    !! done smoothing, or lowess_use_all_gpus(.false.), which does the same.
+    subroutine lowess_release_gpus()
+        integer(int32) :: rc
+        rc = cf_lowess_multi_release()
     end subroutine
 
     !> Reports a non-zero libcurvefit_cuda status through the reference's error
@@ -311,9 +346,10 @@ contains
             return
         end if
         ! lowess(m_x, m_y, f, 2, m_delta = 0, ys, m_weights, m_residuals), :866 --
-        ! range-sharded over every GPU of the box when the series is long enough to be
-        ! worth it (same results: per-point sums never cross devices), else on one
-        if (n >= CF_MULTI_GPU_MIN_POINTS) then
+        ! range-sharded over every GPU of the box when the program opted in
+        ! (lowess_use_all_gpus) and the series is long enough to be worth it (same
+        ! results: per-point sums never cross devices), else on the current device
+        if (m_all_gpus .and. n >= CF_MULTI_GPU_MIN_POINTS) then
             rc = cf_lowess_smooth_multi(this%m_x, this%m_y, n, f, 2_int32, &
                 c_null_ptr, 0_int32, ys, this%m_weights, this%m_residuals)
         else

@@ -102,12 +102,23 @@ CF_API int32_t cf_lowess_smooth_batched(const double* x_sorted, const double* y,
  * cf_lowess_smooth.  devices = NULL or ndev <= 0: all visible devices (at most 8).  One device,
  * or fewer than 4096 points per device: cf_lowess_smooth on devices[0].  The handles and the
  * peer mapping are kept between calls with the same n and device list;
- * cf_lowess_multi_release() frees them.  Calls are serialised per process. */
+ * cf_lowess_multi_release() frees them.  Calls are serialised per process.
+ * No peer access between the devices (PCIe box without P2P, mixed GPUs, MIG), or no room for the
+ * buffers on one of them: the sharded context is freed and the call runs as cf_lowess_smooth on
+ * ONE device (the caller's current device if it is in the list, else the first of the list) --
+ * same results, never an error a single GPU would not also give.  A device list without peer
+ * access is remembered for the life of the process; an out-of-memory one is tried again next call.
+ * cf_lowess_multi_active() = number of devices of the cached sharded context (0: none, i.e. the
+ * last call ran on one GPU or nothing has run).
+ * Memory: every device reserves buffers for all n points (about 60 bytes per point), not only for
+ * its block plus halo -- only the copies shrink with the shard -- so the longest series is the one
+ * a single GPU holds (n = 1e8: 6 GB per device). */
 CF_API int32_t cf_lowess_smooth_multi(const double* x_sorted, const double* y, int32_t n,
                                       double f, int32_t nsteps,
                                       const int32_t* devices, int32_t ndev,
                                       double* ys, double* rw, double* res);
 CF_API int32_t cf_lowess_multi_release(void);
+CF_API int32_t cf_lowess_multi_active(void);
 
 /* ------------------------------------------------------------------------
  * Neighbours of the LOWESS path (stats.cu).

@@ -99,3 +99,41 @@ def test_large_n_delta(cf, oracle):
         assert fit.fitted_points().size < 1000
         assert np.max(np.abs(ys - ref["ys"])) <= TOL * np.max(np.abs(ref["ys"])), method
         assert np.max(np.abs(fit.m_weights - ref["rw"])) <= 1e-9
+
+
+def test_delta_refused_on_a_span_upload(cf):
+    """After cf_lowess_init_span x holds -inf / +inf sentinels outside the uploaded span, so the
+    fitted-point list of delta > 0 (:682-690) cannot be derived from it: both orders of the two
+    calls are refused with CF_INVALID_INPUT_ERROR, and a full init lifts the refusal."""
+    import ctypes as C
+
+    from curvefit_b200 import CF_INVALID_INPUT_ERROR, _lib
+    lib = _lib.load()
+    n = 20_000
+    x = cases.make_x("grid", n)
+    y = cases.make_y(x)
+    xp, yp = x.ctypes.data_as(_lib.c_dp), y.ctypes.data_as(_lib.c_dp)
+    h = C.c_void_p()
+    assert lib.cf_lowess_create(C.byref(h), -1, None) == 0
+    try:
+        # span upload first, delta second
+        assert lib.cf_lowess_init_span(h, xp, yp, n, 5_000, 12_000) == 0
+        assert lib.cf_lowess_set_delta(h, 0.01) == CF_INVALID_INPUT_ERROR
+        buf = C.create_string_buffer(256)
+        lib.cf_last_error(buf, 256)
+        assert b"whole of x" in buf.value
+        assert lib.cf_lowess_delta(h) == 0.0
+        # delta first (on a fully initialised handle), span upload second: the run refuses
+        assert lib.cf_lowess_init(h, xp, yp, n, 0) == 0
+        assert lib.cf_lowess_set_delta(h, 0.01) == 0
+        assert lib.cf_lowess_run(h, 0.1, 1, None) == 0
+        assert lib.cf_lowess_init_span(h, xp, yp, n, 5_000, 12_000) == 0
+        assert lib.cf_lowess_run(h, 0.1, 1, None) == CF_INVALID_INPUT_ERROR
+        # a span that covers everything writes no sentinels and is accepted
+        assert lib.cf_lowess_init_span(h, xp, yp, n, 1, n) == 0
+        assert lib.cf_lowess_run(h, 0.1, 1, None) == 0
+        # delta = 0 on a span upload is unaffected
+        assert lib.cf_lowess_set_delta(h, 0.0) == 0
+        assert lib.cf_lowess_init_span(h, xp, yp, n, 5_000, 12_000) == 0
+    finally:
+        lib.cf_lowess_destroy(h)

@@ -107,6 +107,45 @@ def test_smooth_multi_ties_and_device_lists(oracle):
 
 
 @needs2
+def test_smooth_multi_falls_back_to_one_gpu_when_a_device_is_full():
+    """A GPU that another job has filled must not turn smooth() into an error: the sharded context
+    cannot be built (cudaMalloc fails on device 1), the call runs on one GPU with the same results,
+    and once the memory is free again the next call shards as before."""
+    import torch
+    from curvefit_b200 import _lib
+    lib = _lib.load()
+    n, f, nsteps = 4_000_000, 0.001, 2                         # ~240 MB of buffers per device
+    x = datagen.grid_x(n)
+    y = datagen.noisy_y(x, 5)
+    lib.cf_set_default_method(_lib.CF_METHOD_TREE)
+    hog = None
+    try:
+        lib.cf_lowess_multi_release()
+        one = _smooth(lib.cf_lowess_smooth, x, y, f, nsteps)
+        torch.cuda.init()
+        with torch.cuda.device(1):
+            torch.cuda.empty_cache()
+            free, _ = torch.cuda.mem_get_info()
+            hog = torch.empty(free - (128 << 20), dtype=torch.uint8, device="cuda:1")
+        devs = (C.c_int32 * 2)(0, 1)
+        got = _smooth(lib.cf_lowess_smooth_multi, x, y, f, nsteps, devs, 2)
+        assert lib.cf_lowess_multi_active() == 0               # no sharded context survived
+        for a, b in zip(got, one):
+            assert np.array_equal(a, b)
+        del hog
+        hog = None
+        with torch.cuda.device(1):
+            torch.cuda.empty_cache()
+        again = _smooth(lib.cf_lowess_smooth_multi, x, y, f, nsteps, devs, 2)
+        assert lib.cf_lowess_multi_active() == 2               # out of memory is not remembered
+        assert np.array_equal(again[0], one[0])                # tree evaluator: partition invariant
+    finally:
+        del hog
+        lib.cf_set_default_method(_lib.CF_METHOD_DIRECT)
+        lib.cf_lowess_multi_release()
+
+
+@needs2
 def test_one_process_per_gpu_paths_match_single_gpu():
     """torchrun, 2 ranks: NCCL transport + direct, peer-memory transport + direct / tree, seven
     series each (three of them with delta > 0), every rank compares with its own single-GPU run."""
