@@ -235,6 +235,8 @@ struct cf_lowess {
                                           // fetches the results copies the weights there instead
     double* early_ys = nullptr;           // cf_lowess_smooth: host destinations of ys / res, downloaded chunk by
     double* early_res = nullptr;          //   chunk while the last pass of the tree evaluator is still running
+    bool reserve_only = false;            // launch_fit: size and allocate the evaluator's scratch (partial moments /
+                                          // tree nodes), launch nothing -- multi.cu does this before its host barrier
     bool tree_skip_build = false;         // tree.cu: evaluate only (the pass's tree is built)
     bool tree_build_only = false;         // tree.cu: build only
     // pipelined first pass of cf_lowess_smooth (api.cu): the tree is built chunk by chunk as the

@@ -532,6 +532,7 @@ int launch_variant(cf_lowess* h, FitParams& prm, int sms)
     prm.ksplit = K;
     prm.part = nullptr;
     if (use_cluster) {
+        if (h->reserve_only) return CF_OK;                     // DSMEM variant: no scratch
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3(tiles * K, h->nseries);
         cfg.blockDim = dim3(NT);
@@ -560,6 +561,7 @@ int launch_variant(cf_lowess* h, FitParams& prm, int sms)
         }
         prm.part = h->part;
     }
+    if (h->reserve_only) return CF_OK;
     kern<<<dim3(tiles * K, h->nseries), NT, smem, h->stream>>>(prm);
     CF_CUDA(cudaGetLastError());
     h->launches++;

@@ -209,6 +209,17 @@ int32_t cf_lowess_smooth_multi(const double* x_sorted, const double* y, int32_t 
         cudaStreamSynchronize(h->copy_stream);
         const double t_up = since();
 #endif
+        // Everything the run allocates (candidate list, partial moments / tree nodes) is reserved
+        // here, before the barrier: a rank whose cudaMalloc fails must say so while the others can
+        // still stay out of the collective run -- once they are inside, they would spin in the
+        // device-side peer waits until the timeout, holding g_multi_mu.
+        if (rc == CF_OK) rc = select_prepare(h);
+        if (rc == CF_OK) {
+            h->ns = ns;
+            h->reserve_only = true;
+            rc = launch_fit(h, false);
+            h->reserve_only = false;
+        }
         if (rc != CF_OK) {
             fail(rc);
             std::lock_guard<std::mutex> g(bar.mu);
@@ -242,6 +253,21 @@ int32_t cf_lowess_smooth_multi(const double* x_sorted, const double* y, int32_t 
     work(0);
     for (auto& t : th) t.join();
     cudaSetDevice(caller_dev);
+    if (abort_run) {
+        // nobody entered the collective run.  If all that went wrong is memory (the evaluator's
+        // scratch did not fit beside the buffers on some device), one GPU gets the whole series,
+        // like when the context itself cannot be built.
+        bool only_memory = true;
+        for (int r = 0; r < N; ++r)
+            if (rcs[(size_t)r] != CF_OK && rcs[(size_t)r] != CF_OUT_OF_MEMORY_ERROR) only_memory = false;
+        if (only_memory) {
+            multi_free(g_multi);
+            g_multi = nullptr;
+            for (int d : devs) { if (cudaSetDevice(d) == cudaSuccess) (void)cudaGetLastError(); }
+            lk.unlock();
+            return one_gpu();
+        }
+    }
     for (int r = 0; r < N; ++r) {
         if (rcs[(size_t)r] != CF_OK) {
             set_error("device %d (block %d of %d): %s", devs[(size_t)r], r, N, msgs[(size_t)r].c_str());

@@ -1104,6 +1104,7 @@ int launch_fit_tree(cf_lowess* h, bool use_rw)
         CF_CUDA(cudaMalloc(&h->tree, need));
         h->tree_bytes = need;
     }
+    if (h->reserve_only) return CF_OK;
     prm.nodes = h->tree;
     prm.qsum = h->tree + node_doubles;
     prm.qhdr = prm.qsum + qsum_doubles;
