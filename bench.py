@@ -7,18 +7,22 @@ updates) of the workload, inputs resident in HBM.
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
     torchrun ... bench.py --gpus N ...        (one rank per GPU, N > 1)
 
-The default invocation prints ONE JSON line that carries, at every N:
+The default invocation prints ONE compact JSON line (< 3 kB; what the strings used to explain
+is in DESIGN.md section 6) that carries, at every N:
 
-  value / roofline / e2e   BASELINE configs[1] (n = 1e6, f = 0.05, nsteps = 3) on the DIRECT
-                           kernel -- the O(n ns) sweep the FP64 roofline claim is made on
-  headline_n1e8            the configuration BASELINE.json's metric is quoted on (n = 1e8,
-                           f = 0.05, nsteps = 3, range-sharded over the N ranks) on the
-                           moment-tree evaluator: value, ms_per_step, per-stage ms (max over
-                           ranks), e2e with host buffers, and its deviation from a single-GPU run
-  c4_direct_sample         ONE direct-kernel pass at that geometry (ns = 5e6; 5.5 min in full)
-                           over two waves of strided 512-point tiles per rank, with its own
+  value / ms_per_step / stages / e2e / roofline / vs_single_gpu
+                           the configuration BASELINE.json's metric is quoted on: n = 1e8,
+                           f = 0.05, nsteps = 3, range-sharded over the N ranks, on the
+                           moment-tree evaluator (the product's fastest parity-checked path);
+                           roofline = HBM, 56 B/point/pass against MEASURED_PEAKS.json
+  c2_direct                BASELINE configs[1] (n = 1e6, f = 0.05, nsteps = 3) on the DIRECT
+                           kernel, a complete run: value, e2e, and the FP64 roofline of
+                           cf::fit_kernel -- the O(n ns) sweep north_star's roofline claim is on
+  c4_direct_sample         ONE direct-kernel pass at the headline geometry (ns = 5e6; 5.5 min in
+                           full) over two waves of strided 512-point tiles per rank, with its own
                            roofline fraction and an oracle check at sampled points
-  cpu_baseline (N = 1)     the oracle (C restatement of the reference) on the host cores
+  cpu_baseline (N = 1)     the oracle (C restatement of the reference) on the host cores, on a
+                           bounded sample of output points of the n = 1e8 series
 
 `--workload c2|c4|c5|c3|...` runs a single workload instead (with `--method direct|tree`).
 `--impl reference`: the reference's CPU algorithm (the oracle; the Fortran reference cannot be
@@ -145,11 +149,60 @@ def cpu_sample(x, y, f, nsteps, threads, seconds_target=6.0, robust=True):
             "extrapolated_smooth_s": total_s, "ns_per_pair_per_core": ns_per_pair}
 
 
+def run_reference_default(args):
+    """CPU arm of the default line: the reference's algorithm (the oracle) on the n = 1e8 series.
+    A full smooth is 5e14 (point, element) pairs -- weeks on the host cores -- so every step is a
+    bounded sample of output points, extrapolated (cpu_sample); beside it, BASELINE configs[1]
+    (n = 1e6) is run IN FULL once, all four passes, as a measured like-for-like for `c2_direct`."""
+    from oracle import oracle
+    oracle.build()
+    cores = oracle.host_cores()
+    world = int(os.environ.get("WORLD_SIZE", str(args.gpus)))
+    n, f, nsteps, _ = WORKLOADS["c4"]
+    x, y = make_data(n)
+    for _ in range(max(min(args.warmup, 2), 1)):
+        cpu_sample(x, y, f, nsteps, cores, 0.5, robust=False)
+    t_wall = time.perf_counter()
+    runs = [cpu_sample(x, y, f, nsteps, cores, 3.0, robust=False) for _ in range(max(1, min(args.steps, 5)))]
+    runs.sort(key=lambda r: r["value"])
+    allc = runs[len(runs) // 2]
+    one = cpu_sample(x, y, f, nsteps, 1, 4.0, robust=False)
+    wall = time.perf_counter() - t_wall
+    v = allc["value"]
+    line = {
+        "impl": "reference", "metric": "LOWESS fitted points/sec", "value": v, "unit": "points/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * n / v, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": series_config("c4", "tree", world, args.transport),
+        "cpu_baseline": {"value": v, "unit": "points/s", "cores": allc["cores"], "kind": "port",
+                         "sample": allc["sample"][:200]},
+        "single_thread": {"value": one["value"], "cores": 1},
+        "e2e": {"value": v, "unit": "points/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "timed_region": {"measured_sample_s_per_step": allc["measured_s"], "wall_s_all_steps": wall,
+                         "extrapolated": True},
+        "gpu_launches": 0,
+        "fortran_reference": "not built: no Fortran compiler (oracle/ref/build_ref.sh)",
+    }
+    if not args.no_headline:
+        n2, f2, k2, _ = WORKLOADS["c2"]
+        x2, y2 = make_data(n2)
+        oracle.set_threads(cores)
+        t0 = time.perf_counter()
+        oracle.lowess_mt(x2, y2, f2, k2)
+        dt = time.perf_counter() - t0
+        line["c2_full"] = {"n": n2, "f": f2, "nsteps": k2, "value": n2 / dt, "seconds": dt, "cores": cores,
+                           "extrapolated": False}
+    print(json.dumps(round_floats(line), separators=(",", ":")), flush=True)
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    name = "c2" if args.workload == "default" else args.workload
+    if args.workload == "default":
+        return run_reference_default(args)
+    name = args.workload
     n, f, nsteps, wname = WORKLOADS[name]
     x, y = make_data(n)
     from oracle import oracle
@@ -183,15 +236,6 @@ def run_reference(args):
         "note": "oracle = C restatement of the reference (no Fortran compiler in this image); value = all host "
                 "cores (OpenMP over output points, thread count set explicitly), single_thread beside it",
     }
-    if args.workload == "default" and not args.no_headline:
-        # the metric's own configuration: a handful of points at ns = 5e6 (36 ms per point per core)
-        n4, f4, k4, _ = WORKLOADS["c4"]
-        x4 = np.arange(n4, dtype=np.float64) * (1.0 / (n4 - 1.0))
-        y4 = np.sin(20.0 * x4)
-        r4 = cpu_sample(x4, y4, f4, k4, cores, 3.0, robust=False)
-        line["headline_n1e8"] = {"value": r4["value"], "unit": "points/s", "cores": r4["cores"],
-                                 "extrapolated_smooth_s": r4["extrapolated_smooth_s"], "sample": r4["sample"],
-                                 "note": "direct O(n ns) algorithm of the reference; the |res| sort is not included"}
     print(json.dumps(line), flush=True)
 
 
@@ -539,13 +583,137 @@ def direct_sample(env, fit, stages, x, y, n, f, ns):
     return res
 
 
-def run_ours(args):
+HBM_BYTES_PER_POINT_PASS = 56.0   # x, y, rw read, ys written + the robustness step's share
+# one cf::tree_eval_kernel launch at n = 1e8, ns = 5e6 (profiles/r02_tree_eval_c4_ncu_full.csv)
+NCU_TREE_EVAL = {"dram_bytes": 15.9e9 + 0.8e9, "fp64_pipe_pct": 53.9}
+
+
+def hbm_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "MEASURED_PEAKS.json"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+def tree_roofline(prim, n, nsteps, world):
+    """The tree path against the only bound an O(n log ns) method has: the bytes a pass must move."""
+    passes = nsteps + 1
+    fit_ms = prim["_fit_ms"] / prim["steps"]                       # all passes of one smooth, slowest rank
+    build_ms = prim["stages_ms_per_step"]["tree_build"]
+    eval_ms = (fit_ms - build_ms) / passes                         # one cf::tree_eval_kernel launch
+    peak, src = hbm_peak()
+    ach = HBM_BYTES_PER_POINT_PASS * (n / world) / (eval_ms * 1e-3) / 1e9
+    smooth = HBM_BYTES_PER_POINT_PASS * (n / world) * passes / (prim["ms_per_step"] * 1e-3) / 1e9
+    return {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+            "traffic": NCU_TREE_EVAL["dram_bytes"] if world == 1 else None,
+            "kernel": "cf::tree_eval_kernel", "avg_launch_ms": eval_ms, "per_gpu": True,
+            "share_of_step": eval_ms * passes / prim["ms_per_step"],
+            "whole_smooth_gbs": smooth, "whole_smooth_frac": smooth / peak,
+            "fp64_pipe_pct_ncu": NCU_TREE_EVAL["fp64_pipe_pct"] if world == 1 else None,
+            "peak_source": src}
+
+
+def compact(d, drop=("api", "stages_note", "note", "sample", "algorithmic", "peak_source", "traffic_source",
+                     "workload", "unit", "steps", "warmup", "transport", "x", "y", "l2")):
+    """Nested objects keep numbers only (the driver keeps a 3 kB tail of the line)."""
+    if isinstance(d, dict):
+        return {k: compact(v, drop) for k, v in d.items() if k not in drop and not k.startswith("_")}
+    if isinstance(d, float):
+        return float(f"{d:.6g}")
+    return d
+
+
+def round_floats(d, digits=7):
+    if isinstance(d, dict):
+        return {k: round_floats(v, digits) for k, v in d.items()}
+    if isinstance(d, list):
+        return [round_floats(v, digits) for v in d]
+    if isinstance(d, float):
+        return float(f"{d:.{digits}g}")
+    return d
+
+
+def run_default(args):
+    """The driver's line: top level = the metric's own configuration (n = 1e8, tree), nested =
+    the direct kernel's evidence (C2 in full, one sampled pass at ns = 5e6)."""
     from curvefit_b200 import regression
     env = Env(args)
     rank, world = env.rank, env.world
-    single = args.workload != "default"
-    name = args.workload if single else "c2"
-    method = args.method or ("direct" if not single or name != "c4" else "tree")
+    n, f, nsteps, wname = WORKLOADS["c4"]
+    peak_tf, peak_mhz = regression.fp64_peak(env.local, 300.0)
+    peak_tf = -env.max_over_ranks([-peak_tf])[0]
+    with Clocks(env.local) as clk:
+        head = measure_series(env, "c4", "tree", args.steps, args.warmup, not args.no_e2e,
+                              sample_direct=not args.no_headline, compare_single=True)
+    line = None
+    if rank == 0:
+        line = {
+            "metric": "LOWESS fitted points/sec", "value": head["value"], "unit": "points/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": head["ms_per_step"],
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": series_config("c4", "tree", world, args.transport),
+            "transport_used": head["transport"], "gpu_launches": head["gpu_launches"],
+            "clocks": clk.summary(), "ms_min_max": head["ms_min_max"],
+            "stages_ms_per_step": head["stages_ms_per_step"],
+            "e2e": compact(head["e2e"], drop=("api",)),
+            "roofline": tree_roofline(head, n, nsteps, world),
+        }
+        for k in ("vs_single_gpu", "e2e_c_abi_one_process"):
+            if k in head:
+                line[k] = compact(head[k])
+        if "_direct_sample" in head:
+            ds = head["_direct_sample"]
+            line["c4_direct_sample"] = compact({
+                "tiles_per_rank": ds["tiles_per_rank"], "points_per_rank": ds["points_per_rank"], "ms": ds["ms"],
+                "tflops": ds["roofline"]["achieved"], "peak": ds["roofline"]["peak"], "frac": ds["roofline"]["frac"],
+                "one_pass_s": ds["extrapolated"]["one_pass_s"], "oracle_check": ds.get("oracle_check")})
+    # ---- the direct kernel in full: BASELINE configs[1] ------------------------------------------
+    if not args.no_headline:
+        n2, f2, k2, _ = WORKLOADS["c2"]
+        c2 = measure_series(env, "c2", "direct", args.steps, args.warmup, not args.no_e2e, compare_single=True)
+        if rank == 0:
+            avg_ms = c2["_fit_ms"] / max(c2["fit_launches"], 1)
+            ach = FLOP_PER_PAIR * (n2 / world) * c2["ns"] / (avg_ms * 1e-3) / 1e12
+            line["c2_direct"] = compact({
+                "n": n2, "f": f2, "nsteps": k2, "ns": c2["ns"], "value": c2["value"], "ms_per_step": c2["ms_per_step"],
+                "stages_ms_per_step": c2["stages_ms_per_step"], "gpu_launches": c2["gpu_launches"],
+                "e2e": c2["e2e"], "vs_single_gpu": c2.get("vs_single_gpu"),
+                "roofline": {"bound": "fp64", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s",
+                             "frac": ach / peak_tf if peak_tf else None,
+                             "traffic": NCU_TRAFFIC["c2"]["bytes"] if world == 1 else None,
+                             "kernel": "cf::fit_kernel", "avg_launch_ms": avg_ms,
+                             "share_of_step": c2["_fit_ms"] / (c2["ms_per_step"] * c2["steps"])}})
+    # ---- CPU baseline on the host cores (rank 0, N = 1 only): bounded sample of the n = 1e8 series
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        from oracle import oracle
+        oracle.build()
+        x, y = make_data(n)
+        allc = cpu_sample(x, y, f, nsteps, oracle.host_cores(), 12.0, robust=False)
+        one = cpu_sample(x, y, f, nsteps, 1, 5.0, robust=False)
+        line["cpu_baseline"] = {"value": allc["value"], "unit": "points/s", "cores": allc["cores"], "kind": "port",
+                                "sample": allc["sample"][:160],
+                                "single_thread": {"value": one["value"], "cores": 1}}
+        if "c2_direct" in line:
+            x2, y2 = make_data(WORKLOADS["c2"][0])
+            c = cpu_sample(x2, y2, WORKLOADS["c2"][1], WORKLOADS["c2"][2], oracle.host_cores(), 6.0)
+            line["c2_direct"]["cpu_baseline"] = compact({"value": c["value"], "cores": c["cores"], "kind": "port"})
+    if rank == 0:
+        print(json.dumps(round_floats(line), separators=(",", ":")), flush=True)
+    if world > 1:
+        env.dist.barrier()
+        env.dist.destroy_process_group()
+
+
+def run_ours(args):
+    if args.workload == "default":
+        return run_default(args)
+    from curvefit_b200 import regression
+    env = Env(args)
+    rank, world = env.rank, env.world
+    single = True
+    name = args.workload
+    method = args.method or ("direct" if name != "c4" else "tree")
     n, f, nsteps, wname = WORKLOADS[name]
     peak_tf, peak_mhz = regression.fp64_peak(env.local, 300.0)
     peak_tf = -env.max_over_ranks([-peak_tf])[0]
@@ -600,21 +768,6 @@ def run_ours(args):
                         "roofline claim of this repo is the direct kernel's (c4_direct_sample, or --method direct)"}
         if "_direct_sample" in prim:
             line["c4_direct_sample"] = prim["_direct_sample"]
-
-    # ---- the metric's own configuration: n = 1e8, f = 0.05, nsteps = 3, moment tree, at this N ----
-    if not single and not args.no_headline:
-        hsteps = max(3, min(args.steps, 10))
-        head = measure_series(env, "c4", "tree", hsteps, 3, not args.no_e2e, sample_direct=True,
-                              compare_single=True)
-        if rank == 0:
-            sample = head.pop("_direct_sample", None)
-            head.pop("_fit_ms", None)
-            head["config"] = series_config("c4", "tree", world, args.transport)
-            head["note"] = ("moment-tree evaluator (csrc/tree.cu): the same five sums per point from per-block power "
-                            "moments, equal to the direct kernel to rounding (tolerance 1e-10; tests/test_gpu_tree.py); "
-                            "separate accounting from `value` / `roofline`")
-            line["headline_n1e8"] = head
-            line["c4_direct_sample"] = sample
 
     # ---- CPU baseline on the host cores (rank 0, N = 1 only) ----------------------------
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
