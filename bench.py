@@ -445,7 +445,16 @@ def measure_series(env, name, method, steps, warmup, want_e2e, clocks=None, samp
         out["e2e"] = {"value": n / dt, "unit": "points/s", "h2d_bytes_per_step": 16 * n,
                       "d2h_bytes_per_step": 24 * n, "ms_per_step": dt * 1e3,
                       "api": "cf_lowess_smooth(host x, y -> host ys, rw, res), pinned buffers, wall clock"}
-        del xp, yp, outs
+        # the overlapped host-buffer path (chunked upload, last pass in pieces) against the resident
+        # run of the timed steps above: same series, same evaluator -> the same bits
+        same = True
+        back = np.empty(n)
+        for k, o in enumerate(outs):
+            lib.cf_lowess_fetch(fit._h, *[regression._dp(back) if j == k else None for j in range(3)])
+            same = same and bool(np.array_equal(back, o))
+        out["e2e"]["bitwise_equal_resident"] = same
+        assert same, "cf_lowess_smooth (host buffers) differs from the device-resident run"
+        del xp, yp, outs, back
     elif want_e2e:
         from curvefit_b200.distributed import SharedHostArray
         xp, yp = env.pinned(x), env.pinned(y)

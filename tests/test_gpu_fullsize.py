@@ -79,6 +79,33 @@ def test_c2_full_direct_kernel(cf, oracle):
     _teacher(fit, oracle, x, y, f, rw_in, ys0, 200)
 
 
+@pytest.mark.parametrize("name,n,f,nsteps", [("C2 (BASELINE configs[1])", 1_000_000, 0.05, 3),
+                                             ("C5 scaled (f = 0.8, 5 iterations)", 200_000, 0.8, 5)])
+def test_every_point_against_a_complete_oracle_run(cf, oracle, name, n, f, nsteps):
+    """No teacher forcing: the oracle smooths the WHOLE series on all host cores (lowess_mt, about
+    a minute each) and every one of the n values of ys, rw and res after all nsteps + 1 passes is
+    compared, for both evaluators -- what a user switching from the reference would see."""
+    x = datagen.grid_x(n)
+    y = datagen.noisy_y(x)
+    oracle.set_threads(oracle.host_cores())
+    ref = oracle.lowess_mt(x, y, f, nsteps)
+    scale = float(np.max(np.abs(ref["ys"])))
+    for method in ("direct", "tree"):
+        fit = cf.lowess_smoothing()
+        fit.set_method(method)
+        fit.initialize(x, y, srt=False)
+        ys = fit.smooth(f, nsteps=nsteps)
+        d_ys = float(np.max(np.abs(ys - ref["ys"])))
+        d_res = float(np.max(np.abs(fit.m_residuals - ref["res"])))
+        d_rw = float(np.max(np.abs(fit.m_weights - ref["rw"])))
+        assert d_ys <= TOL * scale, (name, method, d_ys)
+        assert d_res <= TOL * scale, (name, method, d_res)
+        # a weight is a smooth function of res / cmad (slope <= 2 / cmad, cmad ~ 1.5 here) except
+        # for the 4e-6 step at r = .999 cmad (:707-710): nothing sits that close in these series
+        assert d_rw <= 1e-9, (name, method, d_rw)
+        fit.close()
+
+
 def test_c4_full_tree_and_linear_property(cf, oracle):
     """BASELINE headline series: n = 1e8, f = 0.05, 3 robustness iterations (moment-tree
     evaluator; the direct kernel needs > 15 min per smooth at this size)."""
