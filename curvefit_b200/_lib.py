@@ -39,6 +39,7 @@ SIGNATURES = {
     "cf_lowess_span": (C.c_int32, [C.c_int32, C.c_double]),
     "cf_sort_xy": (C.c_int32, [c_dp, c_dp, C.c_int32, c_dp, c_dp, c_ip]),
     "cf_lowess_smooth": (C.c_int32, [c_dp, c_dp, C.c_int32, C.c_double, C.c_int32, c_dp, c_dp, c_dp]),
+    "cf_lowess_smooth_ex": (C.c_int32, [c_dp, c_dp, C.c_int32, C.c_double, C.c_int32, C.c_int32, c_dp, c_dp, c_dp]),
     "cf_lowess_smooth_delta": (C.c_int32, [c_dp, c_dp, C.c_int32, C.c_double, C.c_int32, C.c_double,
                                            c_dp, c_dp, c_dp]),
     "cf_lowess_set_delta": (C.c_int32, [C.c_void_p, C.c_double]),

@@ -185,6 +185,9 @@ static int begin_stage(cf_lowess* h, double f)
 
 // evaluator of handles created from now on and of the stateless calls (cf_set_default_method)
 static std::atomic<int> g_default_method{CF_METHOD_DIRECT};
+// cf_lowess_smooth_ex: evaluator of the stateless call this THREAD is inside (-1: the process default)
+static thread_local int t_call_method = -1;
+int stateless_method() { return t_call_method >= 0 ? t_call_method : g_default_method.load(); }
 
 }  // namespace cf
 
@@ -1028,12 +1031,14 @@ static int32_t pool_acquire(cf_lowess** out)
             if (g_pool[k]->device == dev) {
                 *out = g_pool[k];
                 g_pool.erase(g_pool.begin() + (long)k);
-                (*out)->method = g_default_method.load();
+                (*out)->method = stateless_method();
                 return CF_OK;
             }
         }
     }
-    return cf_lowess_create(out, -1, nullptr);
+    CF_TRY(cf_lowess_create(out, -1, nullptr));
+    (*out)->method = stateless_method();
+    return CF_OK;
 }
 
 static void pool_release(cf_lowess* h, int rc)
@@ -1252,6 +1257,20 @@ int32_t cf_lowess_smooth(const double* x_sorted, const double* y, int32_t n, dou
     rc = body();
     if (rc != CF_OK && h->copy_stream) cudaStreamSynchronize(h->copy_stream);
     pool_release(h, rc);
+    return rc;
+}
+
+int32_t cf_lowess_smooth_ex(const double* x_sorted, const double* y, int32_t n, double f, int32_t nsteps,
+                            int32_t method, double* ys, double* rw, double* res)
+{
+    if (method != CF_METHOD_DIRECT && method != CF_METHOD_TREE && method != CF_METHOD_AUTO) {
+        set_error("method must be CF_METHOD_DIRECT, CF_METHOD_TREE or CF_METHOD_AUTO");
+        return CF_INVALID_INPUT_ERROR;
+    }
+    const int before = t_call_method;
+    t_call_method = method;                    // seen by pool_acquire of this thread only
+    const int32_t rc = cf_lowess_smooth(x_sorted, y, n, f, nsteps, ys, rw, res);
+    t_call_method = before;
     return rc;
 }
 

@@ -268,6 +268,7 @@ int delta_prepare(cf_lowess* h);              // delta.cu: (re)build the fitted-
 int launch_delta_fill(cf_lowess* h);          // delta.cu: tie copy + interpolation + res
 void delta_free(cf_lowess* h);
 // robust.cu: the select of the two middle order statistics of |res| and the weights
+int stateless_method();                                    // api.cu: evaluator of this thread's stateless call
 int select_prepare(cf_lowess* h);                          // (re)allocate the candidate list
 int select_rounds(const cf_lowess* h);                     // W-bit rounds after round 0
 int launch_select(cf_lowess* h, bool fused_residuals);     // passes A-C; single GPU or peer-attached

@@ -182,7 +182,7 @@ int32_t cf_lowess_smooth_multi(const double* x_sorted, const double* y, int32_t 
     MultiCtx* c = g_multi;
     const int N = (int)devs.size();
     const int32_t ns = cf_lowess_span(n, f);
-    const int method = cf_default_method();
+    const int method = stateless_method();      // read on the caller's thread, handed to the rank threads
     std::vector<int> rcs((size_t)N, CF_OK);
     std::vector<std::string> msgs((size_t)N);
     HostBarrier bar;

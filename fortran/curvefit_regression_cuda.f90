@@ -48,6 +48,12 @@ module curvefit_regression_cuda
     !! smoothed on all GPUs of the box (cf_lowess_smooth_multi); shorter ones, and every
     !! series by default, on the current device.
     integer(int32), parameter :: CF_MULTI_GPU_MIN_POINTS = 4000000
+    !> A direct lowest() pass costs n * ns (point, element) pairs, about 1.5e12 of them per second
+    !! on one B200.  From this many pairs per pass on, smooth() asks for the moment tree for that
+    !! call (cf_lowess_smooth_ex with CF_METHOD_TREE: equal to <= 1e-12 relative, contract 1e-10),
+    !! so that a series of 1e8 points is 0.1 s and not 22 minutes; below it the process default
+    !! applies (the direct sweep unless lowess_set_evaluator changed it).
+    real(real64), parameter :: CF_TREE_MIN_PAIRS = 1.0d12
     !> Opt-in switch of the multi-GPU route (process-wide, default off): smooth() behaves
     !! exactly as on a one-GPU box unless the program asks for more.
     logical, save :: m_all_gpus = .false.
@@ -89,6 +95,28 @@ module curvefit_regression_cuda
             integer(c_int32_t), value :: nsteps
             real(c_double), intent(out) :: ys(*), rw(*), res(*)
             integer(c_int32_t) :: rc
+        end function
+
+        ! cf_lowess_smooth with the evaluator given for this call only (thread-local in the
+        ! library; the process default is neither read nor changed)
+        function cf_lowess_smooth_ex(x, y, n, f, nsteps, method, ys, rw, res) &
+                bind(C, name = "cf_lowess_smooth_ex") result(rc)
+            import :: c_int32_t, c_double
+            real(c_double), intent(in) :: x(*), y(*)
+            integer(c_int32_t), value :: n
+            real(c_double), value :: f
+            integer(c_int32_t), value :: nsteps
+            integer(c_int32_t), value :: method
+            real(c_double), intent(out) :: ys(*), rw(*), res(*)
+            integer(c_int32_t) :: rc
+        end function
+
+        ! ns = max(min(int(f * n), n), 2), src/curvefit_regression.f90:647
+        function cf_lowess_span(n, f) bind(C, name = "cf_lowess_span") result(ns)
+            import :: c_int32_t, c_double
+            integer(c_int32_t), value :: n
+            real(c_double), value :: f
+            integer(c_int32_t) :: ns
         end function
 
         ! one series over all (or the listed) GPUs of the box from this one process;
@@ -323,7 +351,7 @@ contains
         class(errors), intent(inout), optional, target :: err
         real(real64), allocatable, dimension(:) :: ys
 
-        integer(int32) :: n, flag, rc
+        integer(int32) :: n, flag, rc, ns
         class(errors), pointer :: errmgr
         type(errors), target :: deferr
 
@@ -353,8 +381,14 @@ contains
             rc = cf_lowess_smooth_multi(this%m_x, this%m_y, n, f, 2_int32, &
                 c_null_ptr, 0_int32, ys, this%m_weights, this%m_residuals)
         else
-            rc = cf_lowess_smooth(this%m_x, this%m_y, n, f, 2_int32, ys, &
-                this%m_weights, this%m_residuals)
+            ns = cf_lowess_span(n, f)
+            if (real(n, real64) * real(ns, real64) >= CF_TREE_MIN_PAIRS) then
+                rc = cf_lowess_smooth_ex(this%m_x, this%m_y, n, f, 2_int32, &
+                    CF_METHOD_TREE, ys, this%m_weights, this%m_residuals)
+            else
+                rc = cf_lowess_smooth(this%m_x, this%m_y, n, f, 2_int32, ys, &
+                    this%m_weights, this%m_residuals)
+            end if
         end if
         if (rc /= 0) call report(errmgr, "ls_smooth", rc)
     end function

@@ -77,6 +77,17 @@ CF_API int32_t cf_lowess_smooth(const double* x_sorted, const double* y, int32_t
                                 double f, int32_t nsteps,
                                 double* ys, double* rw, double* res);
 
+/* cf_lowess_smooth with the evaluator of a lowest() pass given PER CALL (CF_METHOD_DIRECT / _TREE /
+ * _AUTO, below) instead of taken from the process-wide default: the choice is local to the calling
+ * thread and to this call, so two threads can smooth with different evaluators at the same time and
+ * nothing a library deep in the program does with cf_set_default_method changes this call's
+ * numerical path.  No counterpart in the reference (it has one evaluator).  Everything else as
+ * cf_lowess_smooth.  Rule of thumb: a direct pass costs n * ns pairs at about 1.5e12 pairs/s on a
+ * B200 -- beyond n * ns ~ 1e12 choose CF_METHOD_TREE (equal to <= 1e-12 relative). */
+CF_API int32_t cf_lowess_smooth_ex(const double* x_sorted, const double* y, int32_t n,
+                                   double f, int32_t nsteps, int32_t method,
+                                   double* ys, double* rw, double* res);
+
 /* The same with delta > 0 -- lowess's interpolation mode (:674-690): lowest() runs
  * only at points more than delta apart, points in between are linearly interpolated
  * (:675-679), points closer than epsilon to the last fitted one copy it (:685-688).

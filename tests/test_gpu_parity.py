@@ -339,3 +339,46 @@ def test_fewer_than_two_points_return_y_and_touch_nothing_else(cf):
     fit.initialize(np.array([0.25]), np.array([3.5]))
     assert fit.get_count() == 1
     assert np.array_equal(fit.smooth(0.3), np.array([3.5]))
+
+
+def test_per_call_evaluator_from_two_threads():
+    """cf_lowess_smooth_ex: the evaluator is an argument of the call, local to the calling thread.
+    Two threads smooth the same series at the same time, one with the direct sweep and one with the
+    moment tree; each must get exactly what a handle set to its evaluator gives, and the process
+    default must not move."""
+    import threading
+
+    from curvefit_b200 import _lib, lowess_smoothing
+    lib = _lib.load()
+    n, f, nsteps = 300_000, 0.05, 2
+    x = cases.make_x("uniform", n, 11)
+    y = cases.make_y(x, 11)
+    want = {}
+    for name in ("direct", "tree"):
+        fit = lowess_smoothing()
+        fit.set_method(name)
+        fit.initialize(x, y, srt=False)
+        want[name] = fit.smooth(f, nsteps=nsteps).copy()
+        fit.close()
+    assert not np.array_equal(want["direct"], want["tree"])       # else the test could not tell them apart
+    p = lambda a: a.ctypes.data_as(_lib.c_dp)
+    default_before = lib.cf_default_method()
+    bad = []
+
+    def work(name, method):
+        ys, rw, res = np.empty(n), np.empty(n), np.empty(n)
+        for _ in range(6):
+            rc = lib.cf_lowess_smooth_ex(p(x), p(y), n, f, nsteps, method, p(ys), p(rw), p(res))
+            if rc != 0 or not np.array_equal(ys, want[name]):
+                bad.append((name, rc))
+
+    th = [threading.Thread(target=work, args=("direct", _lib.CF_METHOD_DIRECT)),
+          threading.Thread(target=work, args=("tree", _lib.CF_METHOD_TREE))]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    assert not bad, bad
+    assert lib.cf_default_method() == default_before
+    out = np.empty(n)
+    assert lib.cf_lowess_smooth_ex(p(x), p(y), n, f, nsteps, 7, p(out), p(out), p(out)) == 201
